@@ -1,0 +1,157 @@
+/* m3r_abi.h — C ABI of libm3r_b200.so, the B200 (sm_100a) geometric backend that replaces the
+ * reference's `mast3r_slam_backends` CUDA extension.
+ *
+ * Every entry point takes plain DEVICE pointers + sizes + a cudaStream_t (passed as void*).
+ * Nothing here allocates, synchronises the host or throws: all work is enqueued on `stream`
+ * (graph-capturable) and an int status is returned (0 = ok, <0 = M3R_ERR_*).
+ * The torch-facing shim (csrc/bindings.cpp → python module `mast3r_slam_backends`) and the
+ * ctypes wrapper (monst3r-slam_b200/abi.py) are the only callers.
+ *
+ * Reference interface each entry point replaces (paths relative to
+ * /root/reference/MASt3R-SLAM/mast3r_slam/backend/):
+ *   m3r_iter_proj            include/gn.h:89-95   src/gn.cpp:84-99    src/matching_kernels.cu:119-316
+ *   m3r_refine_matches_*     include/gn.h:112-117 src/gn.cpp:101-114  src/matching_kernels.cu:25-116
+ *   m3r_gauss_newton_rays    include/gn.h:45-55   src/gn.cpp:28-52    src/gn_kernels.cu:813-1228
+ *   m3r_gauss_newton_calib   include/gn.h:74-87   src/gn.cpp:54-82    src/gn_kernels.cu:1231-1638
+ *   m3r_gauss_newton_points  include/gn.h:22-31   src/gn.cpp:3-26     src/gn_kernels.cu:455-811
+ *   (index prep gn_kernels.cu:161-170, SparseBlock assemble+solve :57-159 and pose_retr_kernel
+ *    :415-453 run on the device inside the m3r_gauss_newton_* calls.)
+ */
+#ifndef M3R_ABI_H
+#define M3R_ABI_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define M3R_ABI_VERSION 1
+
+/* status codes */
+#define M3R_OK 0
+#define M3R_ERR_BAD_ARG (-1)      /* null pointer / non-positive size / unsupported parameter   */
+#define M3R_ERR_WORKSPACE (-2)    /* workspace too small or misaligned                          */
+#define M3R_ERR_CUDA (-3)         /* a CUDA runtime call failed (see m3r_last_error)            */
+#define M3R_ERR_NCCL (-4)         /* NCCL unavailable or a collective failed                    */
+#define M3R_ERR_UNSUPPORTED (-5)
+
+/* residual kinds of the Gauss-Newton ops */
+#define M3R_GN_POINTS 0
+#define M3R_GN_RAYS 1
+#define M3R_GN_CALIB 2
+
+/* largest keyframe id accepted in ii/jj (device-side compaction uses a presence bitmap) */
+#define M3R_MAX_KF_ID (1 << 20)
+
+int m3r_abi_version(void);
+/* last CUDA / NCCL error text seen by this thread ("" if none) */
+const char* m3r_last_error(void);
+
+/* ---- matching -------------------------------------------------------------------------- */
+
+/* iter_proj: rays_img [b,h,w,9] f32, pts3d_norm [b,n,3] f32, p_init [b,n,2] f32 (u,v)
+ *   -> p_new [b,n,2] f32, converged [b,n] u8 (0/1; torch.bool layout).  Every output element is
+ *   written (n need not be a multiple of the block size; the reference has no guard). */
+int m3r_iter_proj(const float* rays_img, const float* pts3d_norm, const float* p_init,
+                  float* p_new, uint8_t* converged, int b, int h, int w, int n, int max_iter,
+                  float lambda_init, float cost_thresh, void* stream);
+
+/* refine_matches: D11 [b,h,w,fdim], D21 [b,n,fdim], p1 [b,n,2] i64 (u,v) -> p1_new [b,n,2] i64.
+ * The f16 variant reproduces c10::Half arithmetic (every * and + rounded to fp16, k ascending,
+ * best score starts at 0); f32/f64 start at FLT_MIN/DBL_MIN like the reference template. */
+int m3r_refine_matches_f16(const void* D11, const void* D21, const int64_t* p1, int64_t* p1_new,
+                           int b, int h, int w, int n, int fdim, int radius, int dilation_max,
+                           void* stream);
+int m3r_refine_matches_f32(const float* D11, const float* D21, const int64_t* p1, int64_t* p1_new,
+                           int b, int h, int w, int n, int fdim, int radius, int dilation_max,
+                           void* stream);
+int m3r_refine_matches_f64(const double* D11, const double* D21, const int64_t* p1,
+                           int64_t* p1_new, int b, int h, int w, int n, int fdim, int radius,
+                           int dilation_max, void* stream);
+
+/* ---- Gauss-Newton ---------------------------------------------------------------------- */
+
+/* Edge sharding for multi-GPU global optimisation (additive; NULL = single GPU, all edges).
+ * A rank owns directed edges [edge_lo, edge_hi) of the FULL edge list.  idx/valid/Q passed to
+ * the op then hold ONLY those edges' slabs ([edge_hi-edge_lo, n]); ii/jj stay full-length so
+ * every rank derives the same compact indices.  `comm` is an ncclComm_t (from m3r_comm_init);
+ * once per iteration the per-edge 7x7 blocks + 7-vectors (fp64) are all-reduced (sum). */
+typedef struct m3r_gn_shard {
+  int edge_lo;
+  int edge_hi;
+  void* comm;
+} m3r_gn_shard;
+
+typedef struct m3r_gn_params {
+  int kind;            /* M3R_GN_POINTS / RAYS / CALIB                                        */
+  float sigma_a;       /* points: sigma_point | rays: sigma_ray   | calib: sigma_pixel        */
+  float sigma_b;       /* points: unused      | rays: sigma_dist  | calib: sigma_depth        */
+  float C_thresh;
+  float Q_thresh;
+  int max_iter;
+  float delta_thresh;
+  /* calib only */
+  int height, width, pixel_border;
+  float z_eps;
+} m3r_gn_params;
+
+/* bytes of device workspace needed for a problem with num_kf keyframes and num_edges directed
+ * edges (full list) of num_pts points. 256-byte aligned pointer required. */
+size_t m3r_gn_workspace_bytes(int num_kf, int num_edges, int num_pts);
+
+/* Full GN loop, asynchronous on `stream`, zero host round-trips.
+ *   Twc  [num_kf,8] f32  IN/OUT (t, q=xyzw, s), pose 0 fixed (num_fix = 1, gn_kernels.cu:1157)
+ *   Xs   [num_kf,n,3] f32, Cs [num_kf,n] f32, K [3,3] f32 row-major (calib only, else NULL)
+ *   ii,jj [num_edges] i64 keyframe ids (any ids < M3R_MAX_KF_ID; rows of Twc/Xs/Cs are in
+ *         sorted-unique id order exactly as the reference expects)
+ *   idx  [E_local,n] i64, valid [E_local,n] u8, Q [E_local,n] f32
+ *   dx_out [num_kf-1,7] f32 : dx of the last executed iteration (zeros if max_iter == 0)
+ *   info_out (nullable) device int32[4]: {iterations executed, cholesky failures, stopped early,
+ *         bad-index flag}
+ * Non-SPD system => dx = 0 for that iteration, poses untouched (gn_kernels.cu:147-150). */
+int m3r_gauss_newton(float* Twc, const float* Xs, const float* Cs, const float* K,
+                     const int64_t* ii, const int64_t* jj, const int64_t* idx,
+                     const uint8_t* valid, const float* Q, int num_kf, int num_pts,
+                     int num_edges, const m3r_gn_params* params, float* dx_out, int32_t* info_out,
+                     void* workspace, size_t workspace_bytes, const m3r_gn_shard* shard,
+                     void* stream);
+
+/* Building blocks of one GN iteration, exposed for tests / profiling (same stream semantics).
+ * m3r_gn_prepare must be called once per problem before the others (index compaction + the
+ * per-pose incidence lists); it also resets the iteration/stop state. */
+int m3r_gn_prepare(const int64_t* ii, const int64_t* jj, int num_kf, int num_pts, int num_edges,
+                   void* workspace, size_t workspace_bytes, void* stream);
+/* accumulate: writes the per-edge fp64 blocks EB[num_edges][56] = {A_e (7x7 row-major), b_e (7)}
+ * for edges [edge_lo,edge_hi) and zeros for the others (shard == NULL: all edges). */
+int m3r_gn_accumulate(const float* Twc, const float* Xs, const float* Cs, const float* K,
+                      const int64_t* idx, const uint8_t* valid, const float* Q, int num_kf,
+                      int num_pts, int num_edges, const m3r_gn_params* params, void* workspace,
+                      size_t workspace_bytes, const m3r_gn_shard* shard, void* stream);
+/* copy the per-edge blocks out (device double[num_edges*56]) */
+int m3r_gn_edge_blocks(const void* workspace, int num_kf, int num_edges, int num_pts,
+                       double** blocks_out);
+/* assemble + Cholesky + solve + retract + stop test, from the blocks in the workspace */
+int m3r_gn_solve_retract(float* Twc, int num_kf, int num_pts, int num_edges, float delta_thresh,
+                         float* dx_out, int32_t* info_out, void* workspace,
+                         size_t workspace_bytes, void* stream);
+/* reference-layout export of the blocks: Hs [4,E,7,7] f32, gs [2,E,7] f32 (gn_kernels.cu:1096-1137) */
+int m3r_gn_export_hs_gs(const void* workspace, int num_kf, int num_edges, int num_pts, float* Hs,
+                        float* gs, void* stream);
+
+/* pose retraction alone: T_k <- exp(dx[k-num_fix]) * T_k for k >= num_fix (gn_kernels.cu:415-453) */
+int m3r_pose_retr(float* Twc, const float* dx, int num_kf, int num_fix, void* stream);
+
+/* ---- NCCL plumbing (resolved with dlopen; no link-time dependency) ------------------------ */
+#define M3R_NCCL_UNIQUE_ID_BYTES 128
+int m3r_comm_unique_id(void* id_out /* 128 bytes, host */);
+int m3r_comm_init(int rank, int world, const void* id /* 128 bytes, host */, void** comm_out);
+int m3r_comm_destroy(void* comm);
+/* in-place sum all-reduce of `count` doubles (used by the GN loop; exposed for tests) */
+int m3r_comm_allreduce_f64(void* comm, double* buf, size_t count, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* M3R_ABI_H */

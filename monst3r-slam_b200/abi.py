@@ -1,0 +1,208 @@
+"""ctypes binding of libm3r_b200.so (include/m3r_abi.h) operating on torch CUDA tensors.
+
+This is the thinnest possible host layer: it passes `tensor.data_ptr()` and sizes straight to the
+C ABI and never touches the data.  It exists so that tests and bench.py can drive the C ABI
+directly (the torch-free boundary a reference maintainer would bind), next to the pybind module
+`mast3r_slam_backends` that the reference's python code imports.
+
+There is no CPU fallback: if the library is missing, importing this module raises.
+"""
+import ctypes as C
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libm3r_b200.so")
+
+GN_POINTS, GN_RAYS, GN_CALIB = 0, 1, 2
+MAX_KF_ID = 1 << 20
+
+EXPORTS = [
+    "m3r_abi_version", "m3r_last_error", "m3r_iter_proj", "m3r_refine_matches_f16",
+    "m3r_refine_matches_f32", "m3r_refine_matches_f64", "m3r_gn_workspace_bytes", "m3r_gauss_newton",
+    "m3r_gn_prepare", "m3r_gn_accumulate", "m3r_gn_edge_blocks", "m3r_gn_solve_retract",
+    "m3r_gn_export_hs_gs", "m3r_pose_retr", "m3r_comm_unique_id", "m3r_comm_init", "m3r_comm_destroy",
+    "m3r_comm_allreduce_f64",
+]
+
+
+class GnParams(C.Structure):
+    _fields_ = [("kind", C.c_int), ("sigma_a", C.c_float), ("sigma_b", C.c_float),
+                ("C_thresh", C.c_float), ("Q_thresh", C.c_float), ("max_iter", C.c_int),
+                ("delta_thresh", C.c_float), ("height", C.c_int), ("width", C.c_int),
+                ("pixel_border", C.c_int), ("z_eps", C.c_float)]
+
+
+class GnShard(C.Structure):
+    _fields_ = [("edge_lo", C.c_int), ("edge_hi", C.c_int), ("comm", C.c_void_p)]
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python monst3r-slam_b200/build.py` "
+            "(there is no CPU or PyTorch fallback for this backend)")
+    lib = C.CDLL(LIB_PATH)
+    lib.m3r_last_error.restype = C.c_char_p
+    lib.m3r_gn_workspace_bytes.restype = C.c_size_t
+    lib.m3r_gn_workspace_bytes.argtypes = [C.c_int, C.c_int, C.c_int]
+    return lib
+
+
+lib = _load()
+
+
+class M3RError(RuntimeError):
+    pass
+
+
+def _check(rc, what):
+    if rc != 0:
+        raise M3RError(f"{what} failed: code {rc} ({lib.m3r_last_error().decode()})")
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _req(t, name, dtype=None):
+    if not t.is_cuda:
+        raise M3RError(f"{name} must be a CUDA tensor (this backend has no CPU path)")
+    if not t.is_contiguous():
+        raise RuntimeError(f"{name} must be contiguous")
+    if dtype is not None and t.dtype != dtype:
+        raise M3RError(f"{name} must be {dtype}, got {t.dtype}")
+
+
+def iter_proj(rays_img_with_grad, pts_3d_norm, p_init, max_iter, lambda_init, cost_thresh):
+    for t, nm in ((rays_img_with_grad, "rays_img_with_grad"), (pts_3d_norm, "pts_3d_norm"), (p_init, "p_init")):
+        _req(t, nm, torch.float32)
+    b, h, w, c = rays_img_with_grad.shape
+    assert c == 9
+    n = p_init.shape[1]
+    p_new = torch.empty((b, n, 2), dtype=torch.float32, device=p_init.device)
+    conv = torch.empty((b, n), dtype=torch.bool, device=p_init.device)
+    _check(lib.m3r_iter_proj(_ptr(rays_img_with_grad), _ptr(pts_3d_norm), _ptr(p_init), _ptr(p_new),
+                             _ptr(conv), b, h, w, n, int(max_iter), C.c_float(lambda_init),
+                             C.c_float(cost_thresh), _stream()), "m3r_iter_proj")
+    return [p_new, conv]
+
+
+def refine_matches(D11, D21, p1, radius, dilation_max):
+    _req(D11, "D11")
+    _req(D21, "D21", D11.dtype)
+    _req(p1, "p1", torch.int64)
+    b, h, w, fdim = D11.shape
+    n = p1.shape[1]
+    out = torch.empty((b, n, 2), dtype=torch.int64, device=p1.device)
+    fn = {torch.float16: lib.m3r_refine_matches_f16, torch.float32: lib.m3r_refine_matches_f32,
+          torch.float64: lib.m3r_refine_matches_f64}[D11.dtype]
+    _check(fn(_ptr(D11), _ptr(D21), _ptr(p1), _ptr(out), b, h, w, n, fdim, int(radius), int(dilation_max),
+              _stream()), "m3r_refine_matches")
+    return [out]
+
+
+def gn_workspace(num_kf, num_edges, num_pts, device):
+    nbytes = lib.m3r_gn_workspace_bytes(num_kf, num_edges, num_pts)
+    return torch.empty(nbytes, dtype=torch.uint8, device=device), nbytes
+
+
+def make_params(kind, sigma_a, sigma_b, C_thresh, Q_thresh, max_iter, delta_thresh, height=0, width=0,
+                pixel_border=0, z_eps=0.0):
+    return GnParams(kind, sigma_a, sigma_b, C_thresh, Q_thresh, int(max_iter), delta_thresh, int(height),
+                    int(width), int(pixel_border), z_eps)
+
+
+def gauss_newton(params, Twc, Xs, Cs, K, ii, jj, idx, valid, Q, shard=None, workspace=None, info=None,
+                 dx=None):
+    """Full asynchronous GN loop (m3r_gauss_newton).  Twc is updated in place.
+    Returns (dx [N-1,7] f32, info int32[4] device tensor)."""
+    for t, nm, dt in ((Twc, "Twc", torch.float32), (Xs, "Xs", torch.float32), (Cs, "Cs", torch.float32),
+                      (ii, "ii", torch.int64), (jj, "jj", torch.int64), (idx, "idx_ii2jj", torch.int64),
+                      (valid, "valid_match", torch.bool), (Q, "Q", torch.float32)):
+        _req(t, nm, dt)
+    if K is not None:
+        _req(K, "K", torch.float32)
+    N, n = Xs.shape[0], Xs.shape[1]
+    E = ii.shape[0]
+    if workspace is None:
+        workspace, nbytes = gn_workspace(N, E, n, Twc.device)
+    else:
+        nbytes = workspace.numel()
+    if dx is None:
+        dx = torch.empty((N - 1, 7), dtype=torch.float32, device=Twc.device)
+    if info is None:
+        info = torch.empty(4, dtype=torch.int32, device=Twc.device)
+    sh = C.byref(shard) if shard is not None else None
+    _check(lib.m3r_gauss_newton(_ptr(Twc), _ptr(Xs), _ptr(Cs), _ptr(K), _ptr(ii), _ptr(jj), _ptr(idx),
+                                _ptr(valid), _ptr(Q), N, n, E, C.byref(params), _ptr(dx), _ptr(info),
+                                _ptr(workspace), C.c_size_t(nbytes), sh, _stream()), "m3r_gauss_newton")
+    return dx, info
+
+
+def gn_prepare(ii, jj, num_kf, num_pts, workspace):
+    _check(lib.m3r_gn_prepare(_ptr(ii), _ptr(jj), num_kf, num_pts, ii.shape[0], _ptr(workspace),
+                              C.c_size_t(workspace.numel()), _stream()), "m3r_gn_prepare")
+
+
+def gn_accumulate(params, Twc, Xs, Cs, K, idx, valid, Q, num_edges, workspace, shard=None):
+    N, n = Xs.shape[0], Xs.shape[1]
+    sh = C.byref(shard) if shard is not None else None
+    _check(lib.m3r_gn_accumulate(_ptr(Twc), _ptr(Xs), _ptr(Cs), _ptr(K), _ptr(idx), _ptr(valid), _ptr(Q),
+                                 N, n, num_edges, C.byref(params), _ptr(workspace),
+                                 C.c_size_t(workspace.numel()), sh, _stream()), "m3r_gn_accumulate")
+
+
+def gn_export_hs_gs(workspace, num_kf, num_edges, num_pts):
+    Hs = torch.empty((4, num_edges, 7, 7), dtype=torch.float32, device=workspace.device)
+    gs = torch.empty((2, num_edges, 7), dtype=torch.float32, device=workspace.device)
+    _check(lib.m3r_gn_export_hs_gs(_ptr(workspace), num_kf, num_edges, num_pts, _ptr(Hs), _ptr(gs),
+                                   _stream()), "m3r_gn_export_hs_gs")
+    return Hs, gs
+
+
+def gn_edge_blocks(workspace, num_kf, num_edges, num_pts):
+    """fp64 per-edge blocks [E,56] = (A_e 7x7 | b_e 7), copied out of the workspace."""
+    p = C.c_void_p(0)
+    _check(lib.m3r_gn_edge_blocks(_ptr(workspace), num_kf, num_edges, num_pts, C.byref(p)),
+           "m3r_gn_edge_blocks")
+    off = p.value - workspace.data_ptr()
+    return workspace[off: off + num_edges * 56 * 8].view(torch.float64).view(num_edges, 56).clone()
+
+
+def gn_solve_retract(Twc, num_edges, num_pts, delta_thresh, workspace):
+    N = Twc.shape[0]
+    dx = torch.zeros((N - 1, 7), dtype=torch.float32, device=Twc.device)
+    info = torch.zeros(4, dtype=torch.int32, device=Twc.device)
+    _check(lib.m3r_gn_solve_retract(_ptr(Twc), N, num_pts, num_edges, C.c_float(delta_thresh), _ptr(dx),
+                                    _ptr(info), _ptr(workspace), C.c_size_t(workspace.numel()), _stream()),
+           "m3r_gn_solve_retract")
+    return dx, info
+
+
+def pose_retr(Twc, dx, num_fix=1):
+    _req(Twc, "Twc", torch.float32)
+    _req(dx, "dx", torch.float32)
+    _check(lib.m3r_pose_retr(_ptr(Twc), _ptr(dx), Twc.shape[0], int(num_fix), _stream()), "m3r_pose_retr")
+
+
+# ---- NCCL plumbing ------------------------------------------------------------------------------
+def comm_unique_id():
+    buf = C.create_string_buffer(128)
+    _check(lib.m3r_comm_unique_id(buf), "m3r_comm_unique_id")
+    return buf.raw
+
+
+def comm_init(rank, world, uid):
+    comm = C.c_void_p(0)
+    _check(lib.m3r_comm_init(int(rank), int(world), C.c_char_p(uid), C.byref(comm)), "m3r_comm_init")
+    return comm
+
+
+def comm_destroy(comm):
+    _check(lib.m3r_comm_destroy(comm), "m3r_comm_destroy")

@@ -1,0 +1,259 @@
+// C-ABI entry points of the Gauss-Newton path + NCCL plumbing (sm_100a build, host code).
+//
+// Replaces the three host loops gauss_newton_{points,rays,calib}_cuda of
+// mast3r_slam/backend/src/gn_kernels.cu (:725-811, :1140-1228, :1546-1638).  One GN iteration is
+//     [memset non-owned edge blocks] -> accumulate -> [ncclAllReduce of the edge blocks] -> solve
+// all enqueued on the caller's stream; the stop test lives on the device (ctrl[CTRL_DONE]) and later
+// iterations turn into no-ops, so there is no host synchronisation anywhere in the loop.
+#include <dlfcn.h>
+
+#include <cstring>
+#include <mutex>
+#include <string>
+
+#include "gn_common.cuh"
+
+namespace m3r {
+
+static thread_local std::string g_last_error;
+
+void set_last_error(const char* what, cudaError_t err) {
+  g_last_error = std::string(what) + ": " + cudaGetErrorString(err);
+}
+void set_last_error_text(const char* what) { g_last_error = what; }
+
+namespace {
+
+// ---- NCCL through dlopen: torch already maps libnccl.so.2 into the process; no link dependency
+typedef struct { char internal[M3R_NCCL_UNIQUE_ID_BYTES]; } NcclUniqueId;
+typedef int (*fn_GetUniqueId)(NcclUniqueId*);
+typedef int (*fn_CommInitRank)(void**, int, NcclUniqueId, int);
+typedef int (*fn_CommDestroy)(void*);
+typedef int (*fn_AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t);
+typedef const char* (*fn_GetErrorString)(int);
+
+struct NcclApi {
+  void* handle = nullptr;
+  fn_GetUniqueId GetUniqueId = nullptr;
+  fn_CommInitRank CommInitRank = nullptr;
+  fn_CommDestroy CommDestroy = nullptr;
+  fn_AllReduce AllReduce = nullptr;
+  fn_GetErrorString GetErrorString = nullptr;
+  bool ok = false;
+};
+
+NcclApi& nccl() {
+  static NcclApi api;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    const char* names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char* nm : names) {
+      api.handle = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+      if (api.handle) break;
+    }
+    if (!api.handle) return;
+    api.GetUniqueId = (fn_GetUniqueId)dlsym(api.handle, "ncclGetUniqueId");
+    api.CommInitRank = (fn_CommInitRank)dlsym(api.handle, "ncclCommInitRank");
+    api.CommDestroy = (fn_CommDestroy)dlsym(api.handle, "ncclCommDestroy");
+    api.AllReduce = (fn_AllReduce)dlsym(api.handle, "ncclAllReduce");
+    api.GetErrorString = (fn_GetErrorString)dlsym(api.handle, "ncclGetErrorString");
+    api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.AllReduce;
+  });
+  return api;
+}
+
+constexpr int kNcclFloat64 = 8;  // ncclDouble
+constexpr int kNcclSum = 0;      // ncclSum
+
+int nccl_fail(const char* what, int rc) {
+  NcclApi& api = nccl();
+  std::string msg = std::string(what) + ": ";
+  msg += (api.GetErrorString ? api.GetErrorString(rc) : "nccl error");
+  set_last_error_text(msg.c_str());
+  return M3R_ERR_NCCL;
+}
+
+int check_common(int num_kf, int num_pts, int num_edges, const void* ws, size_t ws_bytes, GnLayout* L) {
+  if (num_kf < 2 || num_pts < 1 || num_edges < 1) return M3R_ERR_BAD_ARG;
+  if (!ws || (reinterpret_cast<uintptr_t>(ws) & 255)) return M3R_ERR_WORKSPACE;
+  *L = gn_layout(num_kf, num_edges, num_pts);
+  if (ws_bytes < L->off_total) return M3R_ERR_WORKSPACE;
+  return M3R_OK;
+}
+
+int shard_range(const m3r_gn_shard* shard, int num_edges, int* lo, int* hi) {
+  *lo = 0;
+  *hi = num_edges;
+  if (shard) {
+    *lo = shard->edge_lo;
+    *hi = shard->edge_hi;
+    if (*lo < 0 || *hi > num_edges || *lo > *hi) return M3R_ERR_BAD_ARG;
+  }
+  return M3R_OK;
+}
+
+int accumulate_step(const float* Twc, const float* Xs, const float* Cs, const float* K, const int64_t* idx,
+                    const uint8_t* valid, const float* Q, const GnLayout& L, const GnPtrs& P,
+                    const m3r_gn_params& prm, const m3r_gn_shard* shard, int lo, int hi, cudaStream_t s) {
+  if (shard && (lo > 0 || hi < L.num_edges)) {
+    // non-owned slots must be exact zeros so that the sum all-reduce acts as an all-gather
+    if (lo > 0) M3R_CUDA_CHECK(cudaMemsetAsync(P.eb, 0, sizeof(double) * kEdgeBlock * (size_t)lo, s));
+    if (hi < L.num_edges)
+      M3R_CUDA_CHECK(cudaMemsetAsync(P.eb + (size_t)hi * kEdgeBlock, 0,
+                                     sizeof(double) * kEdgeBlock * (size_t)(L.num_edges - hi), s));
+  }
+  int rc = launch_gn_accumulate(Twc, Xs, Cs, K, idx, valid, Q, L, P, prm, lo, hi, s);
+  if (rc != M3R_OK) return rc;
+  if (shard && shard->comm) {
+    rc = m3r_comm_allreduce_f64(shard->comm, P.eb, (size_t)L.num_edges * kEdgeBlock, s);
+  }
+  return rc;
+}
+
+}  // namespace
+}  // namespace m3r
+
+using namespace m3r;
+
+extern "C" int m3r_abi_version(void) { return M3R_ABI_VERSION; }
+extern "C" const char* m3r_last_error(void) { return g_last_error.c_str(); }
+
+extern "C" size_t m3r_gn_workspace_bytes(int num_kf, int num_edges, int num_pts) {
+  if (num_kf < 2 || num_edges < 1 || num_pts < 1) return 0;
+  return gn_layout(num_kf, num_edges, num_pts).off_total;
+}
+
+extern "C" int m3r_gn_prepare(const int64_t* ii, const int64_t* jj, int num_kf, int num_pts, int num_edges,
+                              void* workspace, size_t workspace_bytes, void* stream) {
+  if (!ii || !jj) return M3R_ERR_BAD_ARG;
+  GnLayout L;
+  int rc = check_common(num_kf, num_pts, num_edges, workspace, workspace_bytes, &L);
+  if (rc != M3R_OK) return rc;
+  return launch_gn_prepare(ii, jj, L, gn_ptrs(L, workspace), static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int m3r_gn_accumulate(const float* Twc, const float* Xs, const float* Cs, const float* K,
+                                 const int64_t* idx, const uint8_t* valid, const float* Q, int num_kf,
+                                 int num_pts, int num_edges, const m3r_gn_params* params, void* workspace,
+                                 size_t workspace_bytes, const m3r_gn_shard* shard, void* stream) {
+  if (!Twc || !Xs || !Cs || !idx || !valid || !Q || !params) return M3R_ERR_BAD_ARG;
+  GnLayout L;
+  int rc = check_common(num_kf, num_pts, num_edges, workspace, workspace_bytes, &L);
+  if (rc != M3R_OK) return rc;
+  int lo, hi;
+  rc = shard_range(shard, num_edges, &lo, &hi);
+  if (rc != M3R_OK) return rc;
+  return accumulate_step(Twc, Xs, Cs, K, idx, valid, Q, L, gn_ptrs(L, workspace), *params, shard, lo, hi,
+                         static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int m3r_gn_edge_blocks(const void* workspace, int num_kf, int num_edges, int num_pts,
+                                  double** blocks_out) {
+  if (!workspace || !blocks_out || num_kf < 2 || num_edges < 1 || num_pts < 1) return M3R_ERR_BAD_ARG;
+  GnLayout L = gn_layout(num_kf, num_edges, num_pts);
+  *blocks_out = gn_ptrs(L, const_cast<void*>(workspace)).eb;
+  return M3R_OK;
+}
+
+extern "C" int m3r_gn_solve_retract(float* Twc, int num_kf, int num_pts, int num_edges, float delta_thresh,
+                                    float* dx_out, int32_t* info_out, void* workspace, size_t workspace_bytes,
+                                    void* stream) {
+  if (!Twc || !dx_out) return M3R_ERR_BAD_ARG;
+  GnLayout L;
+  int rc = check_common(num_kf, num_pts, num_edges, workspace, workspace_bytes, &L);
+  if (rc != M3R_OK) return rc;
+  return launch_gn_solve(Twc, L, gn_ptrs(L, workspace), delta_thresh, dx_out, info_out,
+                         static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int m3r_gn_export_hs_gs(const void* workspace, int num_kf, int num_edges, int num_pts, float* Hs,
+                                   float* gs, void* stream) {
+  if (!workspace || !Hs || !gs || num_kf < 2 || num_edges < 1 || num_pts < 1) return M3R_ERR_BAD_ARG;
+  GnLayout L = gn_layout(num_kf, num_edges, num_pts);
+  return launch_export_hs_gs(L, gn_ptrs(L, const_cast<void*>(workspace)), Hs, gs, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int m3r_pose_retr(float* Twc, const float* dx, int num_kf, int num_fix, void* stream) {
+  if (!Twc || !dx || num_kf < 0 || num_fix < 0) return M3R_ERR_BAD_ARG;
+  return launch_pose_retr(Twc, dx, num_kf, num_fix, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int m3r_gauss_newton(float* Twc, const float* Xs, const float* Cs, const float* K,
+                                const int64_t* ii, const int64_t* jj, const int64_t* idx,
+                                const uint8_t* valid, const float* Q, int num_kf, int num_pts, int num_edges,
+                                const m3r_gn_params* params, float* dx_out, int32_t* info_out, void* workspace,
+                                size_t workspace_bytes, const m3r_gn_shard* shard, void* stream) {
+  if (!Twc || !Xs || !Cs || !ii || !jj || !idx || !valid || !Q || !params || !dx_out) return M3R_ERR_BAD_ARG;
+  if (params->kind == M3R_GN_CALIB && !K) return M3R_ERR_BAD_ARG;
+  if (params->max_iter < 0) return M3R_ERR_BAD_ARG;
+  GnLayout L;
+  int rc = check_common(num_kf, num_pts, num_edges, workspace, workspace_bytes, &L);
+  if (rc != M3R_OK) return rc;
+  int lo, hi;
+  rc = shard_range(shard, num_edges, &lo, &hi);
+  if (rc != M3R_OK) return rc;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  GnPtrs P = gn_ptrs(L, workspace);
+  M3R_CUDA_CHECK(cudaMemsetAsync(dx_out, 0, sizeof(float) * kPose * (size_t)(num_kf - 1), s));
+  if (info_out) M3R_CUDA_CHECK(cudaMemsetAsync(info_out, 0, sizeof(int32_t) * 4, s));
+  rc = launch_gn_prepare(ii, jj, L, P, s);
+  if (rc != M3R_OK) return rc;
+  for (int it = 0; it < params->max_iter; it++) {
+    rc = accumulate_step(Twc, Xs, Cs, K, idx, valid, Q, L, P, *params, shard, lo, hi, s);
+    if (rc != M3R_OK) return rc;
+    rc = launch_gn_solve(Twc, L, P, params->delta_thresh, dx_out, info_out, s);
+    if (rc != M3R_OK) return rc;
+  }
+  return M3R_OK;
+}
+
+// ---------------------------------------------------------------------------------- NCCL plumbing
+extern "C" int m3r_comm_unique_id(void* id_out) {
+  NcclApi& api = nccl();
+  if (!api.ok) {
+    set_last_error_text("libnccl.so.2 not loadable");
+    return M3R_ERR_NCCL;
+  }
+  if (!id_out) return M3R_ERR_BAD_ARG;
+  NcclUniqueId id;
+  int rc = api.GetUniqueId(&id);
+  if (rc != 0) return nccl_fail("ncclGetUniqueId", rc);
+  std::memcpy(id_out, &id, sizeof(id));
+  return M3R_OK;
+}
+
+extern "C" int m3r_comm_init(int rank, int world, const void* id, void** comm_out) {
+  NcclApi& api = nccl();
+  if (!api.ok) {
+    set_last_error_text("libnccl.so.2 not loadable");
+    return M3R_ERR_NCCL;
+  }
+  if (!id || !comm_out || world < 1 || rank < 0 || rank >= world) return M3R_ERR_BAD_ARG;
+  NcclUniqueId uid;
+  std::memcpy(&uid, id, sizeof(uid));
+  void* comm = nullptr;
+  int rc = api.CommInitRank(&comm, world, uid, rank);
+  if (rc != 0) return nccl_fail("ncclCommInitRank", rc);
+  *comm_out = comm;
+  return M3R_OK;
+}
+
+extern "C" int m3r_comm_destroy(void* comm) {
+  NcclApi& api = nccl();
+  if (!api.ok || !comm) return M3R_ERR_BAD_ARG;
+  int rc = api.CommDestroy(comm);
+  if (rc != 0) return nccl_fail("ncclCommDestroy", rc);
+  return M3R_OK;
+}
+
+extern "C" int m3r_comm_allreduce_f64(void* comm, double* buf, size_t count, void* stream) {
+  NcclApi& api = nccl();
+  if (!api.ok) {
+    set_last_error_text("libnccl.so.2 not loadable");
+    return M3R_ERR_NCCL;
+  }
+  if (!comm || !buf) return M3R_ERR_BAD_ARG;
+  int rc = api.AllReduce(buf, buf, count, kNcclFloat64, kNcclSum, comm, static_cast<cudaStream_t>(stream));
+  if (rc != 0) return nccl_fail("ncclAllReduce", rc);
+  return M3R_OK;
+}

@@ -1,0 +1,533 @@
+// On-device linear algebra of the Gauss-Newton loop (sm_100a): index compaction, block-sparse
+// assemble, dense fp64 Cholesky, triangular solves, Sim(3) retraction and the stop test.
+//
+// Replaces HOST code of the reference: get_unique_kf_idx / create_inds (gn_kernels.cu:161-170),
+// SparseBlock::update_lhs / update_rhs / solve with Eigen::SimplicialLLT<double> (:57-159), plus
+// pose_retr_kernel (:415-453) and the linalg_norm().item() stop test (:1219-1222).  The reference
+// does two host round-trips per iteration; here one iteration is  accumulate -> (all-reduce) ->
+// gn_solve_kernel  with no host involvement, so the whole loop can sit in a CUDA graph.
+//
+// gn_solve_kernel (cooperative when the system has more than a few tiles, one CTA otherwise):
+//   A. assemble   each CTA owns pose rows; it zero-fills its 7-row strip of the dense lower
+//                 triangle and adds the incident edge blocks in edge order (deterministic, no atomics)
+//                 H_pp += A_e, H_pq -= A_e (q < p), g_p -+= b_e.  g is stored as one extra row
+//                 below H, so the factorisation also produces y = L^-1 g (bordered-matrix trick).
+//   B. Cholesky   right-looking, 32x32 tiles, fp64: every CTA factors the diagonal tile redundantly
+//                 in shared memory (no broadcast needed), inverts it, and does TRSM on its share of
+//                 the panel as a tile GEMM with L_kk^-1; grid.sync; trailing SYRK/GEMM update tiles
+//                 spread over all CTAs; grid.sync.
+//   C. back-substitution  L^T x = y by CTA 0 with the stored L_kk^-1 tiles, column-parallel.
+//   D. dx = -x (0 if a pivot was <= 0: gn_kernels.cu:142-150), retraction T <- Exp(dx) T in fp32
+//      following :299-413, ||dx|| stop test, next-iteration bookkeeping.
+#include <cooperative_groups.h>
+
+#include "gn_common.cuh"
+
+namespace cg = cooperative_groups;
+
+namespace m3r {
+namespace {
+
+// =============================================================================== prepare kernel
+// compact index of a keyframe id = number of distinct ids below it (== searchsorted(unique(ids)))
+__global__ void __launch_bounds__(1024)
+gn_prepare_kernel(const int64_t* __restrict__ ii, const int64_t* __restrict__ jj, int E, int N,
+                  int* __restrict__ ci, int* __restrict__ cj, unsigned* __restrict__ bitmap,
+                  unsigned* __restrict__ prefix, int* __restrict__ inc_off, int* __restrict__ inc_list,
+                  unsigned* __restrict__ counters, int* __restrict__ ctrl) {
+  constexpr int W = M3R_MAX_KF_ID / 32;
+  const int tid = threadIdx.x, nt = blockDim.x;
+  __shared__ unsigned s_scan[1024];
+  __shared__ int s_bad;
+  if (tid == 0) s_bad = 0;
+  for (int k = tid; k < W; k += nt) bitmap[k] = 0u;
+  for (int k = tid; k < E; k += nt) counters[k] = 0u;
+  if (tid < CTRL_WORDS) ctrl[tid] = 0;
+  __syncthreads();
+  for (int k = tid; k < 2 * E; k += nt) {
+    const int64_t id = k < E ? ii[k] : jj[k - E];
+    if (id < 0 || id >= M3R_MAX_KF_ID) {
+      s_bad = 1;
+    } else {
+      atomicOr(bitmap + (id >> 5), 1u << (id & 31));
+    }
+  }
+  __syncthreads();
+  // exclusive prefix of popcounts over W words: each thread owns W/nt consecutive words
+  const int per = W / nt;  // 32768 / 1024 = 32
+  unsigned local = 0;
+  for (int k = 0; k < per; k++) local += __popc(bitmap[tid * per + k]);
+  s_scan[tid] = local;
+  __syncthreads();
+  for (int off = 1; off < nt; off <<= 1) {
+    unsigned v = tid >= off ? s_scan[tid - off] : 0u;
+    __syncthreads();
+    s_scan[tid] += v;
+    __syncthreads();
+  }
+  unsigned run = s_scan[tid] - local;
+  for (int k = 0; k < per; k++) {
+    prefix[tid * per + k] = run;
+    run += __popc(bitmap[tid * per + k]);
+  }
+  __syncthreads();
+  const unsigned total = s_scan[nt - 1];
+  for (int k = tid; k < E; k += nt) {
+    const int64_t a = ii[k], b = jj[k];
+    int ca = 0, cb = 0;
+    if (a >= 0 && a < M3R_MAX_KF_ID) ca = prefix[a >> 5] + __popc(bitmap[a >> 5] & ((1u << (a & 31)) - 1u));
+    if (b >= 0 && b < M3R_MAX_KF_ID) cb = prefix[b >> 5] + __popc(bitmap[b >> 5] & ((1u << (b & 31)) - 1u));
+    if (ca >= N) { ca = 0; s_bad = 1; }
+    if (cb >= N) { cb = 0; s_bad = 1; }
+    ci[k] = ca;
+    cj[k] = cb;
+  }
+  __syncthreads();
+  if (tid == 0) ctrl[CTRL_BAD] = s_bad | ((total != (unsigned)N) ? 2 : 0);
+  // incidence lists per compact pose c: entries (e << 1 | role) in ascending e; role 0: c == ci[e]
+  // two passes (count, fill); self-edges contribute nothing (H_ii + H_jj - H_ij - H_ji = 0).
+  for (int c = tid; c < N; c += nt) {
+    int cnt = 0;
+    for (int e = 0; e < E; e++) {
+      const int a = ci[e], b = cj[e];
+      if (a != b) cnt += (a == c) + (b == c);
+    }
+    inc_off[c + 1] = cnt;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    inc_off[0] = 0;
+    for (int c = 0; c < N; c++) inc_off[c + 1] += inc_off[c];
+  }
+  __syncthreads();
+  for (int c = tid; c < N; c += nt) {
+    int o = inc_off[c];
+    for (int e = 0; e < E; e++) {
+      const int a = ci[e], b = cj[e];
+      if (a == b) continue;
+      if (a == c) inc_list[o++] = (e << 1) | 0;
+      if (b == c) inc_list[o++] = (e << 1) | 1;
+    }
+  }
+}
+
+// =============================================================================== Sim(3) retraction
+__device__ __forceinline__ void quat_mul(const float* a, const float* b, float* o) {
+  o[0] = a[3] * b[0] + a[0] * b[3] + a[1] * b[2] - a[2] * b[1];
+  o[1] = a[3] * b[1] - a[0] * b[2] + a[1] * b[3] + a[2] * b[0];
+  o[2] = a[3] * b[2] + a[0] * b[1] - a[1] * b[0] + a[2] * b[3];
+  o[3] = a[3] * b[3] - a[0] * b[0] - a[1] * b[1] - a[2] * b[2];
+}
+
+__device__ __forceinline__ void rot_act(const float* q, const float* X, float* Y) {
+  const float u0 = 2.0f * (q[1] * X[2] - q[2] * X[1]);
+  const float u1 = 2.0f * (q[2] * X[0] - q[0] * X[2]);
+  const float u2 = 2.0f * (q[0] * X[1] - q[1] * X[0]);
+  const float y0 = X[0] + q[3] * u0 + (q[1] * u2 - q[2] * u1);
+  const float y1 = X[1] + q[3] * u1 + (q[2] * u0 - q[0] * u2);
+  const float y2 = X[2] + q[3] * u2 + (q[0] * u1 - q[1] * u0);
+  Y[0] = y0; Y[1] = y1; Y[2] = y2;
+}
+
+__device__ __forceinline__ void cross_into(const float* a, float* b) {
+  const float x0 = a[1] * b[2] - a[2] * b[1];
+  const float x1 = a[2] * b[0] - a[0] * b[2];
+  const float x2 = a[0] * b[1] - a[1] * b[0];
+  b[0] = x0; b[1] = x1; b[2] = x2;
+}
+
+// T <- Exp(xi) * T, fp32, same closed form and the same 1e-6 branches as gn_kernels.cu:299-413
+__device__ void sim3_retract(const float* xi, float* T) {
+  float tau[3] = {xi[0], xi[1], xi[2]};
+  const float phi[3] = {xi[3], xi[4], xi[5]};
+  const float sigma = xi[6];
+  const float scale = expf(sigma);
+  const float theta_sq = phi[0] * phi[0] + phi[1] * phi[1] + phi[2] * phi[2];
+  float dq[4];
+  {
+    float imag, real;
+    if (theta_sq < 1e-6f) {
+      const float p4 = theta_sq * theta_sq;
+      imag = 0.5f - (1.0f / 48.0f) * theta_sq + (1.0f / 3840.0f) * p4;
+      real = 1.0f - (1.0f / 8.0f) * theta_sq + (1.0f / 384.0f) * p4;
+    } else {
+      const float th = sqrtf(theta_sq);
+      imag = sinf(0.5f * th) / th;
+      real = cosf(0.5f * th);
+    }
+    dq[0] = imag * phi[0]; dq[1] = imag * phi[1]; dq[2] = imag * phi[2]; dq[3] = real;
+  }
+  const float theta = sqrtf(theta_sq);
+  float A, B, C;
+  if (fabsf(sigma) < 1e-6f) {
+    C = 1.0f;
+    if (fabsf(theta) < 1e-6f) {
+      A = 0.5f;
+      B = 1.0f / 6.0f;
+    } else {
+      A = (1.0f - cosf(theta)) / theta_sq;
+      B = (theta - sinf(theta)) / (theta_sq * theta);
+    }
+  } else {
+    C = (scale - 1.0f) / sigma;
+    if (fabsf(theta) < 1e-6f) {
+      const float s2 = sigma * sigma;
+      A = ((sigma - 1.0f) * scale + 1.0f) / s2;
+      B = (scale * 0.5f * s2 + scale - 1.0f - sigma * scale) / (s2 * sigma);
+    } else {
+      const float a = scale * sinf(theta);
+      const float b = scale * cosf(theta);
+      const float c = theta_sq + sigma * sigma;
+      A = (a * sigma + (1.0f - b) * theta) / (theta * c);
+      B = (C - ((b - 1.0f) * sigma + a * theta) / c) / theta_sq;
+    }
+  }
+  float dt[3] = {C * tau[0], C * tau[1], C * tau[2]};
+  cross_into(phi, tau);
+  dt[0] += A * tau[0]; dt[1] += A * tau[1]; dt[2] += A * tau[2];
+  cross_into(phi, tau);
+  dt[0] += B * tau[0]; dt[1] += B * tau[1]; dt[2] += B * tau[2];
+  float q1[4], t1[3];
+  quat_mul(dq, T + 3, q1);
+  rot_act(dq, T, t1);
+  T[0] = t1[0] * scale + dt[0];
+  T[1] = t1[1] * scale + dt[1];
+  T[2] = t1[2] * scale + dt[2];
+  T[3] = q1[0]; T[4] = q1[1]; T[5] = q1[2]; T[6] = q1[3];
+  T[7] = scale * T[7];
+}
+
+__global__ void pose_retr_kernel(float* __restrict__ Twc, const float* __restrict__ dx, int num_kf, int num_fix) {
+  for (int k = num_fix + blockIdx.x * blockDim.x + threadIdx.x; k < num_kf; k += gridDim.x * blockDim.x) {
+    float T[8], xi[7];
+#pragma unroll
+    for (int c = 0; c < 8; c++) T[c] = Twc[(size_t)k * 8 + c];
+#pragma unroll
+    for (int c = 0; c < 7; c++) xi[c] = dx[(size_t)(k - num_fix) * 7 + c];
+    sim3_retract(xi, T);
+#pragma unroll
+    for (int c = 0; c < 8; c++) Twc[(size_t)k * 8 + c] = T[c];
+  }
+}
+
+// =============================================================================== solve kernel
+struct SolveArgs {
+  float* Twc;
+  const double* eb;
+  const int* ci;
+  const int* cj;
+  const int* inc_off;
+  const int* inc_list;
+  double* hd;
+  double* linv;
+  int* ctrl;
+  float* dx_out;
+  int32_t* info_out;
+  int N, dim, nblk, ld;
+  float delta_thresh;
+};
+
+template <bool COOP>
+__device__ __forceinline__ void grid_barrier() {
+  if (COOP) {
+    cg::this_grid().sync();
+  } else {
+    __syncthreads();
+  }
+}
+
+// factor the 32x32 tile held in Ls (lower, stride 33) in place; returns false on a pivot <= 0
+__device__ bool tile_potrf(double (*Ls)[kTile + 1], int* s_flag) {
+  const int tid = threadIdx.x;
+  if (tid == 0) *s_flag = 0;
+  for (int j = 0; j < kTile; j++) {
+    __syncthreads();
+    if (tid == 0) {
+      const double d = Ls[j][j];
+      if (!(d > 0.0)) {
+        *s_flag = 1;
+        Ls[j][j] = 1.0;
+      } else {
+        Ls[j][j] = sqrt(d);
+      }
+    }
+    __syncthreads();
+    if (tid > j && tid < kTile) Ls[tid][j] /= Ls[j][j];
+    __syncthreads();
+    // trailing update of the tile: entries (r, c) with j < c <= r
+    for (int t = tid; t < kTile * kTile; t += kSolveThreads) {
+      const int r = t >> 5, c = t & 31;
+      if (c > j && c <= r) Ls[r][c] -= Ls[r][j] * Ls[c][j];
+    }
+  }
+  __syncthreads();
+  return *s_flag == 0;
+}
+
+// Li = L^-1 (lower triangular), one column per thread of warp 0
+__device__ void tile_invert(double (*Ls)[kTile + 1], double (*Li)[kTile + 1]) {
+  const int c = threadIdx.x;
+  if (c < kTile) {
+    for (int r = 0; r < kTile; r++) {
+      double s = (r == c) ? 1.0 : 0.0;
+      for (int m = c; m < r; m++) s -= Ls[r][m] * Li[m][c];
+      Li[r][c] = (r < c) ? 0.0 : s / Ls[r][r];
+    }
+  }
+  __syncthreads();
+}
+
+template <bool COOP>
+__global__ void __launch_bounds__(kSolveThreads)
+gn_solve_kernel(const SolveArgs a) {
+  if (a.ctrl[CTRL_DONE]) return;  // uniform over the grid: set only by a previous launch
+  __shared__ double sA[kTile][kTile + 1];
+  __shared__ double sB[kTile][kTile + 1];
+  __shared__ int s_flag;
+  __shared__ double s_red[kSolveThreads / 32];
+  extern __shared__ double s_x[];  // dimP doubles (CTA 0, phase C)
+
+  const int tid = threadIdx.x;
+  const int nblk = a.nblk, ld = a.ld, dim = a.dim, dimP = a.nblk * kTile;
+  double* H = a.hd;
+  const int nfree = a.N - 1;
+
+  // ---------------------------------------------------------------- A. assemble
+  // strips: 0..nfree-1 pose strips (7 rows), then padding rows [dim, dimP), then the rhs tile row
+  const int nstrips = nfree + 2;
+  for (int sidx = blockIdx.x; sidx < nstrips; sidx += gridDim.x) {
+    if (sidx < nfree) {
+      const int p = sidx;
+      const int r0 = 7 * p, ncol = 7 * p + 7;
+      for (int t = tid; t < 7 * ncol; t += kSolveThreads) H[(size_t)(r0 + t / ncol) * ld + (t % ncol)] = 0.0;
+      __syncthreads();
+      const int c = p + 1;  // compact pose index
+      const int lo = a.inc_off[c], hi = a.inc_off[c + 1];
+      for (int q = lo; q < hi; q++) {
+        const int ent = a.inc_list[q];
+        const int e = ent >> 1, role = ent & 1;
+        const int other = (role == 0 ? a.cj[e] : a.ci[e]) - 1;
+        const double* blk = a.eb + (size_t)e * kEdgeBlock;
+        if (tid < 49) {
+          const int r = tid / 7, cc = tid % 7;
+          const double v = blk[tid];
+          H[(size_t)(r0 + r) * ld + (r0 + cc)] += v;
+          if (other >= 0 && other < p) H[(size_t)(r0 + r) * ld + (7 * other + cc)] -= v;
+        }
+      }
+      __syncthreads();
+    } else if (sidx == nfree) {
+      for (int t = tid; t < (dimP - dim) * ld; t += kSolveThreads) {
+        const int r = dim + t / ld, cc = t % ld;
+        H[(size_t)r * ld + cc] = (r == cc) ? 1.0 : 0.0;
+      }
+    } else {
+      // rhs tile row: row dimP holds g, rows dimP+1.. are zero
+      for (int t = tid; t < kTile * ld; t += kSolveThreads) H[(size_t)dimP * ld + t] = 0.0;
+      __syncthreads();
+      for (int p = tid; p < nfree; p += kSolveThreads) {
+        const int c = p + 1;
+        double g[7] = {0, 0, 0, 0, 0, 0, 0};
+        for (int q = a.inc_off[c]; q < a.inc_off[c + 1]; q++) {
+          const int ent = a.inc_list[q];
+          const double* bv = a.eb + (size_t)(ent >> 1) * kEdgeBlock + 49;
+          const double sgn = (ent & 1) ? 1.0 : -1.0;  // g_i = -b_e, g_j = +b_e
+#pragma unroll
+          for (int k = 0; k < 7; k++) g[k] += sgn * bv[k];
+        }
+#pragma unroll
+        for (int k = 0; k < 7; k++) H[(size_t)dimP * ld + 7 * p + k] = g[k];
+      }
+    }
+  }
+  grid_barrier<COOP>();
+
+  // ---------------------------------------------------------------- B. Cholesky
+  bool failed = false;
+  for (int kb = 0; kb < nblk; kb++) {
+    // B1: diagonal tile (redundant per CTA), inverse, TRSM on this CTA's panel tiles
+    for (int t = tid; t < kTile * kTile; t += kSolveThreads) {
+      const int r = t >> 5, c = t & 31;
+      sA[r][c] = (c <= r) ? __ldcg(&H[(size_t)(kb * kTile + r) * ld + kb * kTile + c]) : 0.0;
+    }
+    if (!tile_potrf(sA, &s_flag)) failed = true;
+    tile_invert(sA, sB);  // sB = L_kk^-1
+    if (blockIdx.x == 0) {
+      for (int t = tid; t < kTile * kTile; t += kSolveThreads) {
+        const int r = t >> 5, c = t & 31;
+        a.linv[(size_t)kb * kTile * kTile + t] = sB[r][c];
+        if (c <= r) H[(size_t)(kb * kTile + r) * ld + kb * kTile + c] = sA[r][c];
+      }
+    }
+    for (int I = kb + 1 + blockIdx.x; I <= nblk; I += gridDim.x) {
+      // X = A_Ik * L_kk^-T :  X[r][c] = sum_{m <= c} A[r][m] * Linv[c][m]
+      __syncthreads();
+      for (int t = tid; t < kTile * kTile; t += kSolveThreads)
+        sA[t >> 5][t & 31] = __ldcg(&H[(size_t)(I * kTile + (t >> 5)) * ld + kb * kTile + (t & 31)]);
+      __syncthreads();
+      for (int t = tid; t < kTile * kTile; t += kSolveThreads) {
+        const int r = t >> 5, c = t & 31;
+        double s = 0.0;
+        for (int m = 0; m <= c; m++) s += sA[r][m] * sB[c][m];
+        H[(size_t)(I * kTile + r) * ld + kb * kTile + c] = s;
+      }
+    }
+    grid_barrier<COOP>();
+    // B2: trailing update  A_IJ -= L_Ik * L_Jk^T  for kb < J <= I <= nblk (J < nblk)
+    const int rem = nblk - kb;          // tile rows below kb, including the rhs row
+    const int ncols = rem - 1;          // tile columns kb+1 .. nblk-1
+    // tiles enumerated row by row: row i (1..rem) has min(i, ncols) tiles
+    const int ntiles = ncols * (ncols + 1) / 2 + ncols;  // triangle + rhs row
+    for (int t0 = blockIdx.x; t0 < ntiles; t0 += gridDim.x) {
+      int i, j;
+      if (t0 < ncols * (ncols + 1) / 2) {
+        // invert the triangular number: i = row (0-based within triangle), j <= i
+        i = (int)((sqrt(8.0 * (double)t0 + 1.0) - 1.0) * 0.5);
+        while ((i + 1) * (i + 2) / 2 <= t0) i++;
+        while (i * (i + 1) / 2 > t0) i--;
+        j = t0 - i * (i + 1) / 2;
+      } else {
+        i = ncols;  // rhs row
+        j = t0 - ncols * (ncols + 1) / 2;
+      }
+      const int I = kb + 1 + i, J = kb + 1 + j;
+      __syncthreads();
+      for (int t = tid; t < kTile * kTile; t += kSolveThreads) {
+        const int r = t >> 5, c = t & 31;
+        sA[r][c] = __ldcg(&H[(size_t)(I * kTile + r) * ld + kb * kTile + c]);
+        sB[r][c] = __ldcg(&H[(size_t)(J * kTile + r) * ld + kb * kTile + c]);
+      }
+      __syncthreads();
+      // thread -> 2x2 outputs: rows r, r+16 ; cols c, c+16
+      {
+        const int r = tid >> 4, c = tid & 15;
+        double acc00 = 0, acc01 = 0, acc10 = 0, acc11 = 0;
+#pragma unroll 8
+        for (int m = 0; m < kTile; m++) {
+          const double a0 = sA[r][m], a1 = sA[r + 16][m], b0 = sB[c][m], b1 = sB[c + 16][m];
+          acc00 += a0 * b0; acc01 += a0 * b1; acc10 += a1 * b0; acc11 += a1 * b1;
+        }
+        double* o = &H[(size_t)(I * kTile) * ld + J * kTile];
+        o[(size_t)r * ld + c] = __ldcg(&o[(size_t)r * ld + c]) - acc00;
+        o[(size_t)r * ld + c + 16] = __ldcg(&o[(size_t)r * ld + c + 16]) - acc01;
+        o[(size_t)(r + 16) * ld + c] = __ldcg(&o[(size_t)(r + 16) * ld + c]) - acc10;
+        o[(size_t)(r + 16) * ld + c + 16] = __ldcg(&o[(size_t)(r + 16) * ld + c + 16]) - acc11;
+      }
+    }
+    grid_barrier<COOP>();
+  }
+  if (blockIdx.x != 0) return;
+
+  // ---------------------------------------------------------------- C. back-substitution (CTA 0)
+  for (int t = tid; t < dimP; t += kSolveThreads) s_x[t] = __ldcg(&H[(size_t)dimP * ld + t]);  // y = L^-1 g
+  __syncthreads();
+  for (int kb = nblk - 1; kb >= 0; kb--) {
+    // x_kb = L_kk^-T s_kb : x[c] = sum_{m >= c} Linv[m][c] * s[m]
+    double xv = 0.0;
+    if (tid < kTile) {
+      const double* Li = a.linv + (size_t)kb * kTile * kTile;
+      for (int m = tid; m < kTile; m++) xv += Li[m * kTile + tid] * s_x[kb * kTile + m];
+    }
+    __syncthreads();
+    if (tid < kTile) s_x[kb * kTile + tid] = xv;
+    __syncthreads();
+    // s[col] -= sum_r L[kb*32 + r][col] * x_kb[r]   for col < kb*32
+    for (int col = tid; col < kb * kTile; col += kSolveThreads) {
+      double s = 0.0;
+#pragma unroll 8
+      for (int r = 0; r < kTile; r++) s += __ldcg(&H[(size_t)(kb * kTile + r) * ld + col]) * s_x[kb * kTile + r];
+      s_x[col] -= s;
+    }
+    __syncthreads();
+  }
+
+  // ---------------------------------------------------------------- D. dx, retraction, stop test
+  double ss = 0.0;
+  for (int t = tid; t < dim; t += kSolveThreads) {
+    const float d = failed ? 0.0f : (float)(-s_x[t]);
+    a.dx_out[t] = d;
+    ss += (double)d * (double)d;
+  }
+  for (int off = 16; off > 0; off >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, off);
+  if ((tid & 31) == 0) s_red[tid >> 5] = ss;
+  __syncthreads();
+  for (int k = 1 + tid; k < a.N; k += kSolveThreads) {
+    float T[8], xi[7];
+#pragma unroll
+    for (int c = 0; c < 8; c++) T[c] = a.Twc[(size_t)k * 8 + c];
+#pragma unroll
+    for (int c = 0; c < 7; c++) xi[c] = failed ? 0.0f : (float)(-s_x[(k - 1) * 7 + c]);
+    sim3_retract(xi, T);
+#pragma unroll
+    for (int c = 0; c < 8; c++) a.Twc[(size_t)k * 8 + c] = T[c];
+  }
+  if (tid == 0) {
+    double tot = 0.0;
+    for (int w = 0; w < kSolveThreads / 32; w++) tot += s_red[w];
+    const float nrm = (float)sqrt(tot);
+    a.ctrl[CTRL_ITERS] += 1;
+    if (failed) a.ctrl[CTRL_FAILS] += 1;
+    if (nrm < a.delta_thresh) {
+      a.ctrl[CTRL_DONE] = 1;
+      a.ctrl[CTRL_EARLY] = 1;
+    }
+    if (a.info_out) {
+      a.info_out[0] = a.ctrl[CTRL_ITERS];
+      a.info_out[1] = a.ctrl[CTRL_FAILS];
+      a.info_out[2] = a.ctrl[CTRL_EARLY];
+      a.info_out[3] = a.ctrl[CTRL_BAD];
+    }
+  }
+}
+
+int g_coop_grid = -1;  // CTAs that can be co-resident for the cooperative variant (per process)
+
+}  // namespace
+
+int launch_gn_prepare(const int64_t* ii, const int64_t* jj, const GnLayout& L, const GnPtrs& P, cudaStream_t s) {
+  gn_prepare_kernel<<<1, 1024, 0, s>>>(ii, jj, L.num_edges, L.num_kf, P.ci, P.cj, P.bitmap, P.prefix,
+                                       P.inc_off, P.inc_list, P.counters, P.ctrl);
+  M3R_LAUNCH_CHECK();
+  return M3R_OK;
+}
+
+int launch_gn_solve(float* Twc, const GnLayout& L, const GnPtrs& P, float delta_thresh, float* dx_out,
+                    int32_t* info_out, cudaStream_t s) {
+  SolveArgs a{};
+  a.Twc = Twc; a.eb = P.eb; a.ci = P.ci; a.cj = P.cj; a.inc_off = P.inc_off; a.inc_list = P.inc_list;
+  a.hd = P.hd; a.linv = P.linv; a.ctrl = P.ctrl; a.dx_out = dx_out; a.info_out = info_out;
+  a.N = L.num_kf; a.dim = L.dim; a.nblk = L.nblk; a.ld = L.ld; a.delta_thresh = delta_thresh;
+  const size_t dyn = sizeof(double) * (size_t)L.nblk * kTile;
+  if (dyn > 160 * 1024) return M3R_ERR_UNSUPPORTED;  // > 20k unknowns: out of scope for a dense solve
+  if (L.nblk < 3) {
+    gn_solve_kernel<false><<<1, kSolveThreads, dyn, s>>>(a);
+    M3R_LAUNCH_CHECK();
+    return M3R_OK;
+  }
+  if (dyn > 48 * 1024 - 20 * 1024) {
+    M3R_CUDA_CHECK(cudaFuncSetAttribute(gn_solve_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+  }
+  if (g_coop_grid < 0) {
+    int dev = 0, sms = 0, per_sm = 0;
+    M3R_CUDA_CHECK(cudaGetDevice(&dev));
+    M3R_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    M3R_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gn_solve_kernel<true>, kSolveThreads, dyn));
+    if (per_sm < 1) return M3R_ERR_UNSUPPORTED;
+    g_coop_grid = sms;  // one CTA per SM: the grid barrier cost grows with the CTA count
+  }
+  int grid = g_coop_grid;
+  const int max_useful = L.nblk * (L.nblk + 1) / 2 + L.nblk;
+  if (grid > max_useful) grid = max_useful;
+  void* args[] = {(void*)&a};
+  M3R_CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)gn_solve_kernel<true>, dim3(grid), dim3(kSolveThreads), args, dyn, s));
+  return M3R_OK;
+}
+
+int launch_pose_retr(float* Twc, const float* dx, int num_kf, int num_fix, cudaStream_t s) {
+  if (num_kf <= num_fix) return M3R_OK;
+  pose_retr_kernel<<<(num_kf - num_fix + 127) / 128, 128, 0, s>>>(Twc, dx, num_kf, num_fix);
+  M3R_LAUNCH_CHECK();
+  return M3R_OK;
+}
+
+}  // namespace m3r

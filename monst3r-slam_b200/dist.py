@@ -1,0 +1,61 @@
+"""Multi-GPU global optimisation: edge partitioner + communicator setup.
+
+The keyframe graph is partitioned across ranks BY DIRECTED EDGE: rank r owns a contiguous range of
+the (two-way) edge list and holds only those edges' slabs (idx / valid / Q, 13 B per point per edge,
+96 % of the bytes); Xs / Cs / Twc are replicated.  Once per Gauss-Newton iteration the per-edge
+7x7 + 7 fp64 blocks are all-reduced (sum over zero-padded disjoint slots, so the result is exact and
+bit-identical on every rank) and every rank runs the same deterministic solve + retraction.
+One process per GPU; torch.distributed is only used to ship the 128-byte NCCL unique id.
+"""
+import ctypes as C
+
+
+def partition_edges(num_edges, world, rank=None):
+    """Balanced contiguous ranges over the directed edge list.  -> [(lo, hi)] or (lo, hi) for `rank`."""
+    base, rem = divmod(int(num_edges), int(world))
+    out, lo = [], 0
+    for r in range(world):
+        hi = lo + base + (1 if r < rem else 0)
+        out.append((lo, hi))
+        lo = hi
+    return out if rank is None else out[rank]
+
+
+def shard_edge_tensors(lo, hi, *tensors):
+    """slice per-edge slabs (first dim = directed edge) to the owned range, contiguous"""
+    return tuple(t[lo:hi].contiguous() for t in tensors)
+
+
+def pair_aligned_order(ii, jj):
+    """Permutation of the directed edge list that puts both directions of a pair next to each other
+    and orders pairs by min(i, j): a contiguous shard then touches a compact keyframe range."""
+    import torch
+    a = torch.minimum(ii, jj)
+    b = torch.maximum(ii, jj)
+    big = int(max(int(b.max().item()) + 1, 1))
+    key = (a * big + b) * 2 + (ii > jj).long()
+    return torch.argsort(key, stable=True)
+
+
+def init_comm(rank, world, device=None, group=None):
+    """Create the backend's own NCCL communicator.  Needs torch.distributed to be initialised (any
+    backend) to broadcast the unique id from rank 0.  Returns an abi.GnShard-compatible handle."""
+    import torch
+    import torch.distributed as dist
+    from . import abi
+    if device is not None:
+        torch.cuda.set_device(device)
+    if rank == 0:
+        uid = abi.comm_unique_id()
+    else:
+        uid = bytes(128)
+    if world > 1:
+        box = [uid]
+        dist.broadcast_object_list(box, src=0, group=group)
+        uid = box[0]
+    return abi.comm_init(rank, world, uid)
+
+
+def make_shard(lo, hi, comm=None):
+    from . import abi
+    return abi.GnShard(int(lo), int(hi), comm if comm is not None else C.c_void_p(0))
