@@ -208,3 +208,63 @@ def make_graph(num_kf=32, num_und_edges=120, h=384, w=512, seed=1003, device="cp
         Xs32 = (rays.float() * Xs32[..., 2:3]).contiguous()
     return dict(Twc_gt=Twc_gt.float(), Twc=Twc.float().contiguous(), Xs=Xs32.contiguous(), Cs=Cs, K=K.float().to(dev),
                 ii=ii.to(dev), jj=jj.to(dev), idx=idx, valid=valid, Q=Q, h=h, w=w)
+
+
+def make_graph_exact(num_kf=4, num_und_edges=5, n=768, seed=7, device="cpu", noise=0.0, valid_prob=0.9,
+                     perturb=(0.02, 0.01, 0.01), h=None, w=None, calib=False):
+    """Small well-conditioned graph for parity tests: every keyframe sees the same n world points
+    under its own random pixel permutation, so correspondences are exact (plus optional gaussian
+    noise) and the gather index is non-trivial.  With `calib`, n must be h*w: points are the
+    back-projection of the pixel grid of each camera at random depth, matched through world space
+    is impossible exactly, so calib uses camera 0's grid re-observed by nearby cameras and keeps the
+    identity permutation (targets are pixel centres)."""
+    g = _gen(seed)
+    dev = torch.device(device)
+    ident = torch.tensor([0, 0, 0, 0, 0, 0, 1, 1], dtype=torch.float64)
+    poses = [ident] + [_rand_pose(g, (0.3, 0.3, 0.1), 6.0, 0.9, 1.1) for _ in range(num_kf - 1)]
+    Twc_gt = torch.stack(poses)
+    W = torch.randn(n, 3, generator=g, dtype=torch.float64) * torch.tensor([0.8, 0.6, 0.4], dtype=torch.float64)
+    W = W + torch.tensor([0.0, 0.0, 3.0], dtype=torch.float64)
+    perms = [torch.arange(n)] + [torch.randperm(n, generator=g) for _ in range(num_kf - 1)]
+    if calib:
+        perms = [torch.arange(n) for _ in range(num_kf)]
+    Xs = torch.empty(num_kf, n, 3, dtype=torch.float64)
+    for k in range(num_kf):
+        Xc = sim3_act(sim3_inv(Twc_gt[k]), W)
+        Xs[k, perms[k]] = Xc + noise * torch.randn(n, 3, generator=g, dtype=torch.float64)
+    und = [(k, k + 1) for k in range(min(num_kf - 1, num_und_edges))]
+    seen = set(und)
+    while len(und) < num_und_edges:
+        a, b_ = sorted(torch.randint(0, num_kf, (2,), generator=g).tolist())
+        if a != b_ and (a, b_) not in seen:
+            seen.add((a, b_))
+            und.append((a, b_))
+    ii = torch.tensor([e[0] for e in und] + [e[1] for e in und], dtype=torch.int64)
+    jj = torch.tensor([e[1] for e in und] + [e[0] for e in und], dtype=torch.int64)
+    E2 = ii.numel()
+    inv = [torch.empty(n, dtype=torch.int64) for _ in range(num_kf)]
+    for k in range(num_kf):
+        inv[k][perms[k]] = torch.arange(n)
+    idx = torch.stack([perms[ii[e]][inv[jj[e]]] for e in range(E2)])  # pixel k of j -> pixel of i
+    valid = (torch.rand(E2, n, 1, generator=g) < valid_prob)
+    Q = torch.exp(1.0 + 0.5 * torch.randn(E2, n, 1, generator=g)).float()
+    Cs = (1.0 + torch.exp(torch.randn(num_kf, n, 1, generator=g))).float()
+    Twc = Twc_gt.clone()
+    st, sr, ss = perturb
+    for k in range(1, num_kf):
+        d = torch.cat((st * torch.randn(3, generator=g, dtype=torch.float64),
+                       torch.zeros(4, dtype=torch.float64), torch.zeros(1, dtype=torch.float64)))
+        dw = sr * torch.randn(3, generator=g, dtype=torch.float64)
+        ang = dw.norm()
+        dq = torch.cat((dw / ang * torch.sin(ang / 2), torch.cos(ang / 2)[None]))
+        es = torch.exp(ss * torch.randn(1, generator=g, dtype=torch.float64))
+        Tk = Twc_gt[k]
+        x1, y1, z1, w1 = dq
+        x2, y2, z2, w2 = Tk[3:7]
+        q_new = torch.stack((w1 * x2 + x1 * w2 + y1 * z2 - z1 * y2, w1 * y2 - x1 * z2 + y1 * w2 + z1 * x2,
+                             w1 * z2 + x1 * y2 - y1 * x2 + z1 * w2, w1 * w2 - x1 * x2 - y1 * y2 - z1 * z2))
+        Twc[k] = torch.cat((es * (quat_to_R(dq) @ Tk[0:3]) + d[0:3], q_new, es * Tk[7:8]))
+    K = intrinsics(h, w) if (h and w) else intrinsics(24, 32)
+    out = dict(Twc_gt=Twc_gt.float(), Twc=Twc.float().contiguous(), Xs=Xs.float().contiguous(), Cs=Cs, K=K,
+               ii=ii, jj=jj, idx=idx.contiguous(), valid=valid, Q=Q, h=h, w=w)
+    return {k_: (v.to(dev) if torch.is_tensor(v) else v) for k_, v in out.items()}

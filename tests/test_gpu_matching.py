@@ -1,0 +1,153 @@
+"""GPU parity of iter_proj / refine_matches (through the C ABI) against the CPU oracle and, when
+oracle/_ref/ref_backends.so is present, against the reference's own CUDA kernels on the same box.
+Bar (BASELINE.json): indices / masks identical on >= 99.9 % of pixels, every disagreement <= 1 px;
+fp16 refine is integer/fp16 arithmetic and must be bit exact.
+"""
+import numpy as np
+import pytest
+import torch
+
+from conftest import match_agreement, need_gpu, np_, pkg
+
+pytestmark = pytest.mark.gpu
+CFG = pkg("matching").DEFAULT_CFG
+
+
+def _prep(synth, h, w, seed, b=1, init="identity"):
+    d = synth.make_matching_pair(h, w, b=b, seed=seed, device="cuda")
+    m = pkg("matching")
+    rays, pts, p0 = m.prep_for_iter_proj(d["X11"], d["X21"], None if init == "identity" else d["idx_init"])
+    return d, rays, pts, p0
+
+
+@pytest.mark.parametrize("init", ["identity", "previous"])
+def test_iter_proj_vs_oracle(backends, oracle, synth, init):
+    need_gpu()
+    d, rays, pts, p0 = _prep(synth, 96, 128, 21, b=2, init=init)
+    p, c = backends.iter_proj(rays, pts, p0, CFG["max_iter"], CFG["lambda_init"], CFG["convergence_thresh"])
+    po, co = oracle.iter_proj(np_(rays), np_(pts), np_(p0), CFG["max_iter"], CFG["lambda_init"], CFG["convergence_thresh"])
+    same, worst = match_agreement(np_(p.long()), po.astype(np.int64))
+    assert same >= 0.999 and worst <= 1, (same, worst)
+    assert (np_(c) == co).mean() >= 0.999
+    assert np.abs(np_(p) - po).max() < 0.05
+
+
+@pytest.mark.parametrize("b", [1, 2])
+def test_iter_proj_vs_reference_cuda_full_size(backends, ref_backends, synth, b):
+    need_gpu()
+    d, rays, pts, p0 = _prep(synth, 384, 512, 1001, b=b)
+    args = (rays, pts, p0, CFG["max_iter"], CFG["lambda_init"], CFG["convergence_thresh"])
+    p, c = backends.iter_proj(*args)
+    pr, cr = ref_backends.iter_proj(*args)
+    same, worst = match_agreement(np_(p.long()), np_(pr.long()))
+    bitwise = (p == pr).all(-1).float().mean().item()
+    print(f"iter_proj vs reference CUDA: long-identical {same:.6f}, worst {worst}px, bitwise {bitwise:.6f}")
+    assert same >= 0.999 and worst <= 1
+    assert (c == cr).float().mean().item() >= 0.999
+
+
+def test_iter_proj_ragged_n_and_zero_iter(backends, oracle, synth):
+    need_gpu()
+    d, rays, pts, p0 = _prep(synth, 48, 64, 5)
+    n = 1001  # not a multiple of any block size; the reference would read out of bounds here
+    p, c = backends.iter_proj(rays, pts[:, :n].contiguous(), p0[:, :n].contiguous(), 10, 1e-8, 1e-6)
+    po, co = oracle.iter_proj(np_(rays), np_(pts[:, :n]), np_(p0[:, :n]), 10, 1e-8, 1e-6)
+    assert p.shape == (1, n, 2)
+    assert match_agreement(np_(p.long()), po.astype(np.int64))[0] >= 0.999
+    p, c = backends.iter_proj(rays, pts, p0 - 5.0, 0, 1e-8, 1e-6)
+    assert not c.any() and p.min() >= 1.0
+
+
+def test_iter_proj_identity_known_answer(backends, synth):
+    """X21 = X11 and identity init -> identity indices, converged."""
+    need_gpu()
+    d = synth.make_matching_pair(96, 128, seed=3, device="cuda", flow_amp=0.0)
+    m = pkg("matching")
+    rays, pts, p0 = m.prep_for_iter_proj(d["X11"], d["X11"], None)
+    p, c = backends.iter_proj(rays, pts, p0, 10, 1e-8, 1e-6)
+    inner = (p0[..., 0] >= 1) & (p0[..., 0] <= 126) & (p0[..., 1] >= 1) & (p0[..., 1] <= 94)
+    assert (p.round().long() == p0.long())[inner].all()
+    assert c[inner].float().mean() > 0.999
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.float32, torch.float64])
+def test_refine_vs_oracle(backends, oracle, synth, dtype):
+    need_gpu()
+    h, w = 96, 128
+    d, rays, pts, p0 = _prep(synth, h, w, 22, b=2)
+    p1 = pkg("matching").lin_to_pixel(d["idx_init"], w)
+    D11 = d["D11"].to(dtype)
+    D21 = d["D21"].view(2, h * w, -1).to(dtype)
+    (out,) = backends.refine_matches(D11, D21, p1, 3, 5)
+    want = oracle.refine_matches(np_(D11), np_(D21), np_(p1), 3, 5)
+    if dtype == torch.float16:
+        assert np.array_equal(np_(out), want)
+    else:
+        same, worst = match_agreement(np_(out), want)
+        assert same >= 0.999
+
+
+def test_refine_borders_zero_descriptors_generic_fdim(backends, oracle):
+    need_gpu()
+    g = torch.Generator().manual_seed(5)
+    h, w = 40, 56
+    for fdim in (24, 16):
+        D11 = torch.randn(1, h, w, fdim, generator=g).half().cuda()
+        D21 = torch.randn(1, 500, fdim, generator=g).half().cuda()
+        # starts on and next to every border
+        u = torch.randint(0, w, (500,), generator=g)
+        v = torch.randint(0, h, (500,), generator=g)
+        u[:50] = 0; u[50:100] = w - 1; v[100:150] = 0; v[150:200] = h - 1
+        p1 = torch.stack((u, v), -1)[None].cuda()
+        (out,) = backends.refine_matches(D11, D21, p1, 3, 5)
+        want = oracle.refine_matches(np_(D11), np_(D21), np_(p1), 3, 5)
+        assert np.array_equal(np_(out), want), fdim
+        assert out[..., 0].min() >= 0 and out[..., 0].max() < w and out[..., 1].max() < h
+        (out0,) = backends.refine_matches(torch.zeros_like(D11), D21, p1, 3, 5)
+        assert torch.equal(out0, p1)
+    for radius, dil in ((1, 1), (2, 3), (3, 0), (4, 2)):
+        (out,) = backends.refine_matches(D11, D21, p1, radius, dil)
+        want = oracle.refine_matches(np_(D11), np_(D21), np_(p1), radius, dil)
+        assert np.array_equal(np_(out), want), (radius, dil)
+
+
+def test_refine_vs_reference_cuda_full_size(backends, ref_backends, synth):
+    need_gpu()
+    h, w = 384, 512
+    d, rays, pts, p0 = _prep(synth, h, w, 1001)
+    p1 = pkg("matching").lin_to_pixel(d["idx_init"], w)
+    D11 = d["D11"].half()
+    D21 = d["D21"].view(1, h * w, -1).half()
+    (out,) = backends.refine_matches(D11, D21, p1, 3, 5)
+    (want,) = ref_backends.refine_matches(D11, D21, p1, 3, 5)
+    assert torch.equal(out, want)
+
+
+def test_match_pipeline_vs_reference_cuda(backends, ref_backends, synth):
+    """matching.match end to end (torch glue + both ops), ours vs the reference's kernels."""
+    need_gpu()
+    m = pkg("matching")
+    d = synth.make_matching_pair(384, 512, seed=1001, device="cuda")
+    for init in (None, d["idx_init"]):
+        idx_a, val_a = m.match(d["X11"], d["X21"], d["D11"], d["D21"], init, ops=backends)
+        idx_b, val_b = m.match(d["X11"], d["X21"], d["D11"], d["D21"], init, ops=ref_backends)
+        pa, pb = m.lin_to_pixel(idx_a, 512), m.lin_to_pixel(idx_b, 512)
+        same, worst = match_agreement(np_(pa), np_(pb))
+        assert same >= 0.999, same
+        assert (val_a == val_b).float().mean().item() >= 0.999
+        # sanity: the matches are close to the planted flow where valid
+        gt_u, gt_v = d["pu"].view(1, -1), d["pv"].view(1, -1)
+        err = torch.maximum((pa[..., 0] - gt_u).abs(), (pa[..., 1] - gt_v).abs())[val_a[..., 0]]
+        assert err.median() <= 1.5
+
+
+def test_drop_in_module_equals_c_abi(backends, synth):
+    need_gpu()
+    mod = pkg().load_drop_in()
+    d, rays, pts, p0 = _prep(synth, 96, 128, 9)
+    a = backends.iter_proj(rays, pts, p0, 10, 1e-8, 1e-6)
+    b = mod.iter_proj(rays, pts, p0, 10, 1e-8, 1e-6)
+    assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1]) and b[1].dtype == torch.bool
+    p1 = a[0].long()
+    D11, D21 = d["D11"].half(), d["D21"].view(1, 96 * 128, -1).half()
+    assert torch.equal(backends.refine_matches(D11, D21, p1, 3, 5)[0], mod.refine_matches(D11, D21, p1, 3, 5)[0])
