@@ -296,3 +296,188 @@ def run_gpu(args):
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def run_global_opt(args, abi, synth, mdist, dev, rank, world, barrier, max_over_ranks, peak):
+    """Multi-keyframe gauss_newton_rays (config 3) / gauss_newton_calib (config 4), directed edges
+    sharded over the ranks (SURVEY §8e): every rank holds Xs/Cs/Twc and ONLY its own edges' slabs;
+    one NCCL all-reduce of the fp64 edge blocks per iteration; strong scaling (the graph is fixed)."""
+    import torch
+    cfg = {"c3": dict(N=32, E=120, calib=False, seed=1003), "c4": dict(N=256, E=1000, calib=True, seed=1004)}[args.global_opt]
+    g = synth.make_graph(cfg["N"], cfg["E"], H, W, seed=cfg["seed"], device=dev, calib=cfg["calib"])
+    N, n, E2 = cfg["N"], N_PX, 2 * cfg["E"]
+    order = mdist.pair_aligned_order(g["ii"], g["jj"])
+    ii, jj = g["ii"][order].contiguous(), g["jj"][order].contiguous()
+    lo, hi = mdist.partition_edges(E2, world, rank)
+    own = order[lo:hi]
+    idx, valid, Q = g["idx"][own].contiguous(), g["valid"][own].contiguous(), g["Q"][own].contiguous()
+    del g["idx"], g["valid"], g["Q"]
+    torch.cuda.empty_cache()
+    comm = mdist.init_comm(rank, world, dev) if world > 1 else None
+    shard = mdist.make_shard(lo, hi, comm) if world > 1 else None
+    iters = 10
+    if cfg["calib"]:
+        prm = abi.make_params(abi.GN_CALIB, 1.0, 10.0, 0.0, 1.5, iters, 0.0, H, W, -10, 1e-6)
+        K = g["K"].contiguous()
+    else:
+        prm = abi.make_params(abi.GN_RAYS, 0.003, 10.0, 0.0, 1.5, iters, 0.0)
+        K = None
+    ws, _ = abi.gn_workspace(N, E2, n, dev)
+    Twc = g["Twc"].clone()
+    dx = torch.empty((N - 1, 7), dtype=torch.float32, device=dev)
+    info = torch.empty(4, dtype=torch.int32, device=dev)
+
+    def solve():
+        Twc.copy_(g["Twc"])
+        abi.gauss_newton(prm, Twc, g["Xs"], g["Cs"], K, ii, jj, idx, valid, Q, shard=shard, workspace=ws, info=info, dx=dx)
+
+    reps = max(3, min(args.steps, 10))
+    for _ in range(3):
+        solve()
+    barrier()
+    ts = []
+    for _ in range(reps):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        a.record()
+        solve()
+        b.record()
+        b.synchronize()
+        ts.append(a.elapsed_time(b))
+    ms = max_over_ranks(statistics.median(ts))
+    # accumulate alone (rank-local, no collective) for the roofline of the sharded kernel
+    abi.gn_prepare(ii, jj, N, n, ws)
+    sh_local = mdist.make_shard(lo, hi, None) if world > 1 else None
+    ta = []
+    for r in range(3 + reps):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        abi.gn_accumulate(prm, g["Twc"], g["Xs"], g["Cs"], K, idx, valid, Q, E2, ws, shard=sh_local)
+        b.record()
+        b.synchronize()
+        if r >= 3:
+            ta.append(a.elapsed_time(b))
+    acc_ms = max_over_ranks(statistics.median(ta))
+    touched = int(torch.unique(torch.cat((ii[lo:hi], jj[lo:hi]))).numel())
+    nbytes = gn_bytes(hi - lo, touched)
+    gerr = float((Twc - g["Twc_gt"]).abs().max().item())
+    if comm is not None:
+        torch.cuda.synchronize()
+        abi.comm_destroy(comm)
+    return {"config": f"configs[{2 if args.global_opt == 'c3' else 3}]: {N} keyframes / {E2} directed edges, 512x384, "
+                      f"{'gauss_newton_calib' if cfg['calib'] else 'gauss_newton_rays'} x{iters} iters",
+            "scaling": "strong", "n_gpus": world, "ms_per_solve": ms, "iters": iters,
+            "gn_edge_iters_per_s": E2 * iters / (ms * 1e-3), "accumulate_ms_per_iter": acc_ms,
+            "accumulate_GBps_per_gpu": nbytes / (acc_ms * 1e-3) / 1e9,
+            "accumulate_frac_of_hbm_peak": nbytes / (acc_ms * 1e-3) / 1e9 / peak,
+            "accumulate_bytes_per_rank": nbytes, "solve_and_comm_ms_per_iter": ms / iters - acc_ms,
+            "collective": "ncclAllReduce(sum, f64) of the [E2,56] edge blocks, once per iteration" if world > 1 else None,
+            "max_abs_pose_err_vs_gt": gerr,
+            "working_set": "13 B/pt/edge slabs (>= 0.6 GB per rank at c3/8) exceed the 126 MB L2; not flushed"}
+
+
+# ------------------------------------------------------------------------------------------ CPU arm
+def _np(t):
+    return t.detach().cpu().numpy()
+
+
+def cpu_reference_step(inp, steps=1, warmup=0, budget_s=25.0):
+    """The reference's CPU path for one tracking step, timed on this box's host cores: the reference's
+    own iter_proj / refine_matches kernel source built for the host (oracle/_ref/libref_matching_host.so,
+    kind "reference") and the line-by-line host port of ray_align_kernel + Eigen-equivalent fp64 solve
+    (oracle/cpu_oracle.cpp, kind "port": the reference's GN has no host build — Eigen + CUDA kernel).
+    Bounded sample: the first `n_s` of the 196 608 query pixels for matching and `it_s` of the 10 GN
+    iterations, sized from a calibration pass so one step fits `budget_s`; scaled to whole steps."""
+    import numpy as np
+    from oracle import oracle as orc
+    cores = os.cpu_count() or 1
+    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    impl = "reference" if orc.have_ref_host() else "port"
+    rays, pts, p0 = _np(inp["rays"]), _np(inp["pts"]), _np(inp["p0"])
+    D11, D21 = _np(inp["D11"]), _np(inp["D21"])
+    gn = [_np(inp[k]) for k in ("Twc0", "Xs", "Cs", "ii", "jj", "idx", "valid", "Q")]
+
+    def matching(n_s):
+        t0 = time.perf_counter()
+        p, _ = orc.iter_proj(rays, pts[:, :n_s], p0[:, :n_s], MATCH_CFG["max_iter"], MATCH_CFG["lambda_init"],
+                             MATCH_CFG["convergence_thresh"], impl=impl)
+        t1 = time.perf_counter()
+        orc.refine_matches(D11, D21[:, :n_s], p.astype(np.int64), MATCH_CFG["radius"], MATCH_CFG["dilation_max"], impl=impl)
+        t2 = time.perf_counter()
+        return t1 - t0, t2 - t1
+
+    def gn_run(it_s):
+        t0 = time.perf_counter()
+        orc.gauss_newton_rays(*gn, GN_RAYS["sigma_ray"], GN_RAYS["sigma_dist"], GN_RAYS["C_thresh"], GN_RAYS["Q_thresh"],
+                              it_s, GN_RAYS["delta_thresh"])
+        return time.perf_counter() - t0
+
+    # calibration: 1/16 of the pixels, 1 GN iteration
+    n_c = N_PX // 16
+    ti, tr = matching(n_c)
+    tg = gn_run(1)
+    full = (ti + tr) * 16 + tg * GN_RAYS["max_iter"]
+    frac = min(1.0, budget_s / full) if full > 0 else 1.0
+    n_s = max(4096, min(N_PX, int(N_PX * frac) // 1024 * 1024))
+    it_s = max(1, min(GN_RAYS["max_iter"], int(round(GN_RAYS["max_iter"] * frac))))
+    est = []
+    parts = None
+    for s in range(warmup + steps):
+        ti, tr = matching(n_s)
+        tg = gn_run(it_s)
+        step_s = (ti + tr) * (N_PX / n_s) + tg * (GN_RAYS["max_iter"] / it_s)
+        if s >= warmup:
+            est.append(step_s)
+            parts = {"iter_proj_s": ti * N_PX / n_s, "refine_matches_s": tr * N_PX / n_s,
+                     "gauss_newton_rays_s": tg * GN_RAYS["max_iter"] / it_s}
+    step_s = statistics.median(est)
+    return {"value": N_PX / step_s, "unit": "px/s", "cores": cores,
+            "kind": "reference" if impl == "reference" else "port",
+            "sample": f"{n_s} of {N_PX} query px through the reference's matching kernels built for the host "
+                      f"({impl}) + {it_s} of {GN_RAYS['max_iter']} GN iterations (N=2, E2=2, all {N_PX} points) "
+                      f"through the host port of ray_align_kernel + fp64 LLT; scaled to one whole step",
+            "s_per_step": step_s, "parts_s_per_step": parts}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path for the same step, on the host cores of this box."""
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if rank != 0:
+        return
+    import torch
+    _, _, synth, matching, _ = load_pkg()  # synth + torch glue only: no kernel of ours is on this path
+    inp = make_tracking_inputs(synth, matching, torch.device("cpu"), 1001)
+    K, Wm = args.steps, args.warmup
+    budget = max(4.0, min(25.0, 150.0 / max(1, K + Wm)))
+    cpu = cpu_reference_step(inp, steps=K, warmup=Wm, budget_s=budget)
+    line = {"impl": "reference", "metric": METRIC, "value": cpu["value"], "unit": "px/s", "n_gpus": world,
+            "steps": K, "warmup": Wm, "ms_per_step": cpu["s_per_step"] * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32 / f16 (c10::Half on host) / f64 solve", "data": "synthetic",
+            "config": {"workload": "configs[1]: frame-to-keyframe tracking, 512x384, 24-d desc, matching + "
+                                   "gauss_newton_rays N=2/E2=2 x10 iters; reference CPU path, rank 0 only",
+                       "parallelism": f"host cores x{cpu['cores']} (OpenMP)"},
+            "cpu_baseline": cpu,
+            "e2e": {"value": cpu["value"], "unit": "px/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--global-opt", default="c3", choices=["c3", "c4", "none"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()
