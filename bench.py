@@ -200,7 +200,8 @@ def run_gpu(args):
     total_ms = max_over_ranks(sum(ts))
     ms_per_step = total_ms / K
     value = world * N_PX / (ms_per_step * 1e-3)
-    launches_per_step = 1 + 1 + 1 + 2 * GN_RAYS["max_iter"]  # iter_proj, refine, gn_prepare, 10x(accum+solve)
+    # iter_proj, refine, gn_prepare, gn_pack, 10 x gn_accum (the small solve + retraction ride in its last CTA)
+    launches_per_step = 1 + 1 + 1 + 1 + GN_RAYS["max_iter"]
 
     # ---- per-kernel timings for the roofline (rank 0 numbers; kernels timed alone, cold L2) -------
     peak, peak_kind = peaks()
@@ -215,8 +216,18 @@ def run_gpu(args):
     def k_refine():
         abi.refine_matches(inp["D11"], inp["D21"], p1_fixed, 3, 5)
 
+    abi.gn_pack(prm, inp["Cs"], inp["idx"], inp["valid"], inp["Q"], N, E2, ws)
+
+    def k_pack():
+        abi.gn_pack(prm, inp["Cs"], inp["idx"], inp["valid"], inp["Q"], N, E2, ws)
+
     def k_accum():
-        abi.gn_accumulate(prm, inp["Twc0"], inp["Xs"], inp["Cs"], None, inp["idx"], inp["valid"], inp["Q"], E2, ws)
+        abi.gn_accumulate_packed(prm, inp["Twc0"], inp["Xs"], None, E2, ws)
+
+    def k_gn():
+        Twc.copy_(inp["Twc0"])
+        abi.gauss_newton(prm, Twc, inp["Xs"], inp["Cs"], None, inp["ii"], inp["jj"], inp["idx"], inp["valid"],
+                         inp["Q"], workspace=ws, info=info, dx=dx)
 
     Ttmp = inp["Twc0"].clone()
 
@@ -227,8 +238,11 @@ def run_gpu(args):
     reps = max(K, 10)
     for name, fn, nbytes, per_step in (("iter_proj_kernel", k_iter, BYTES_ITER_PROJ * N_PX, 1),
                                        ("refine_f16_fd24_kernel", k_refine, BYTES_REFINE * N_PX, 1),
-                                       ("gn_accum_kernel<rays>", k_accum, gn_bytes(E2, N), GN_RAYS["max_iter"]),
-                                       ("gn_solve_kernel", k_solve, 0, GN_RAYS["max_iter"])):
+                                       ("gn_pack_kernel (inside gauss_newton)", k_pack, (13 + 8) * E2 * n + 8 * N * n, 0),
+                                       ("gn_accum_kernel<rays> (accumulate only, cold L2)", k_accum, gn_bytes(E2, N), 0),
+                                       ("gn_small_solve_kernel (stand-alone)", k_solve, 0, 0),
+                                       ("gauss_newton_rays x10 (prepare + pack + 10 fused accumulate/solve launches)",
+                                        k_gn, gn_bytes(E2, N) * GN_RAYS["max_iter"], 1)):
         t = timed(fn, reps, 3)
         ms = statistics.median(t)
         kern[name] = {"ms": ms, "launches_per_step": per_step, "bytes": nbytes,
@@ -236,6 +250,7 @@ def run_gpu(args):
                       "frac_of_hbm_peak": (nbytes / (ms * 1e-3) / 1e9 / peak) if nbytes else None,
                       "share_of_step": ms * per_step / ms_per_step}
     abi.gn_prepare(inp["ii"], inp["jj"], N, n, ws)
+    abi.gn_pack(prm, inp["Cs"], inp["idx"], inp["valid"], inp["Q"], N, E2, ws)
     dom = max(kern, key=lambda k_: kern[k_]["share_of_step"] if kern[k_]["bytes"] else -1)
     roofline = {"kernel": dom, "bound": "hbm", "achieved": kern[dom]["GBps"], "peak": peak, "unit": "GB/s",
                 "frac": kern[dom]["frac_of_hbm_peak"], "traffic": None, "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs)",
@@ -322,7 +337,7 @@ def run_global_opt(args, abi, synth, mdist, dev, rank, world, barrier, max_over_
     else:
         prm = abi.make_params(abi.GN_RAYS, 0.003, 10.0, 0.0, 1.5, iters, 0.0)
         K = None
-    ws, _ = abi.gn_workspace(N, E2, n, dev)
+    ws, _ = abi.gn_workspace(N, E2, n, dev, edges_local=hi - lo)
     Twc = g["Twc"].clone()
     dx = torch.empty((N - 1, 7), dtype=torch.float32, device=dev)
     info = torch.empty(4, dtype=torch.int32, device=dev)
@@ -348,16 +363,20 @@ def run_global_opt(args, abi, synth, mdist, dev, rank, world, barrier, max_over_
     # accumulate alone (rank-local, no collective) for the roofline of the sharded kernel
     abi.gn_prepare(ii, jj, N, n, ws)
     sh_local = mdist.make_shard(lo, hi, None) if world > 1 else None
-    ta = []
+    ta, tp = [], []
     for r in range(3 + reps):
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a, b, c = (torch.cuda.Event(enable_timing=True) for _ in range(3))
         a.record()
-        abi.gn_accumulate(prm, g["Twc"], g["Xs"], g["Cs"], K, idx, valid, Q, E2, ws, shard=sh_local)
+        abi.gn_pack(prm, g["Cs"], idx, valid, Q, N, E2, ws, shard=sh_local)
         b.record()
-        b.synchronize()
+        abi.gn_accumulate_packed(prm, g["Twc"], g["Xs"], K, E2, ws, shard=sh_local)
+        c.record()
+        c.synchronize()
         if r >= 3:
-            ta.append(a.elapsed_time(b))
+            tp.append(a.elapsed_time(b))
+            ta.append(b.elapsed_time(c))
     acc_ms = max_over_ranks(statistics.median(ta))
+    pack_ms = max_over_ranks(statistics.median(tp))
     touched = int(torch.unique(torch.cat((ii[lo:hi], jj[lo:hi]))).numel())
     nbytes = gn_bytes(hi - lo, touched)
     gerr = float((Twc - g["Twc_gt"]).abs().max().item())
@@ -370,7 +389,10 @@ def run_global_opt(args, abi, synth, mdist, dev, rank, world, barrier, max_over_
             "gn_edge_iters_per_s": E2 * iters / (ms * 1e-3), "accumulate_ms_per_iter": acc_ms,
             "accumulate_GBps_per_gpu": nbytes / (acc_ms * 1e-3) / 1e9,
             "accumulate_frac_of_hbm_peak": nbytes / (acc_ms * 1e-3) / 1e9 / peak,
-            "accumulate_bytes_per_rank": nbytes, "solve_and_comm_ms_per_iter": ms / iters - acc_ms,
+            "accumulate_bytes_per_rank": nbytes, "pack_ms_per_solve": pack_ms,
+            "accumulate_plus_amortised_pack_frac_of_hbm_peak": nbytes / ((acc_ms + pack_ms / iters) * 1e-3) / 1e9 / peak,
+            "accumulate_streamed_bytes_per_rank": 8 * (hi - lo) * n + 12 * touched * n,
+            "solve_and_comm_ms_per_iter": (ms - pack_ms) / iters - acc_ms,
             "collective": "ncclAllReduce(sum, f64) of the [E2,56] edge blocks, once per iteration" if world > 1 else None,
             "max_abs_pose_err_vs_gt": gerr,
             "working_set": "13 B/pt/edge slabs (>= 0.6 GB per rank at c3/8) exceed the 126 MB L2; not flushed"}

@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define M3R_ABI_VERSION 1
+#define M3R_ABI_VERSION 2
 
 /* status codes */
 #define M3R_OK 0
@@ -100,6 +100,9 @@ typedef struct m3r_gn_params {
 /* bytes of device workspace needed for a problem with num_kf keyframes and num_edges directed
  * edges (full list) of num_pts points. 256-byte aligned pointer required. */
 size_t m3r_gn_workspace_bytes(int num_kf, int num_edges, int num_pts);
+/* same for a rank that owns only `edges_local` of the edges (the 8 B/pt packed slabs, the bulk of
+ * the workspace, are kept for owned edges only) */
+size_t m3r_gn_workspace_bytes_sharded(int num_kf, int num_edges, int num_pts, int edges_local);
 
 /* Full GN loop, asynchronous on `stream`, zero host round-trips.
  *   Twc  [num_kf,8] f32  IN/OUT (t, q=xyzw, s), pose 0 fixed (num_fix = 1, gn_kernels.cu:1157)
@@ -123,11 +126,18 @@ int m3r_gauss_newton(float* Twc, const float* Xs, const float* Cs, const float* 
  * per-pose incidence lists); it also resets the iteration/stop state. */
 int m3r_gn_prepare(const int64_t* ii, const int64_t* jj, int num_kf, int num_pts, int num_edges,
                    void* workspace, size_t workspace_bytes, void* stream);
-/* accumulate: writes the per-edge fp64 blocks EB[num_edges][56] = {A_e (7x7 row-major), b_e (7)}
- * for edges [edge_lo,edge_hi) and zeros for the others (shard == NULL: all edges). */
-int m3r_gn_accumulate(const float* Twc, const float* Xs, const float* Cs, const float* K,
-                      const int64_t* idx, const uint8_t* valid, const float* Q, int num_kf,
-                      int num_pts, int num_edges, const m3r_gn_params* params, void* workspace,
+/* pack: folds everything that does not depend on the poses (valid_match, Q > Q_thresh, C_i[m] and
+ * C_j[k] > C_thresh, sqrt(Q)) into one 8-byte record per (owned edge, point) in the workspace.
+ * Once per problem, after m3r_gn_prepare; the iterations then stream 8 B/pt/edge instead of 13 B
+ * plus two confidence reads. */
+int m3r_gn_pack(const float* Cs, const int64_t* idx, const uint8_t* valid, const float* Q,
+                int num_kf, int num_pts, int num_edges, const m3r_gn_params* params,
+                void* workspace, size_t workspace_bytes, const m3r_gn_shard* shard, void* stream);
+/* accumulate (after m3r_gn_pack): writes the per-edge fp64 blocks EB[num_edges][56] =
+ * {A_e (7x7 row-major), b_e (7)} for edges [edge_lo,edge_hi) and zeros for the others
+ * (shard == NULL: all edges); all-reduces them when shard->comm is set. */
+int m3r_gn_accumulate(const float* Twc, const float* Xs, const float* K, int num_kf, int num_pts,
+                      int num_edges, const m3r_gn_params* params, void* workspace,
                       size_t workspace_bytes, const m3r_gn_shard* shard, void* stream);
 /* copy the per-edge blocks out (device double[num_edges*56]) */
 int m3r_gn_edge_blocks(const void* workspace, int num_kf, int num_edges, int num_pts,

@@ -20,8 +20,8 @@ MAX_KF_ID = 1 << 20
 
 EXPORTS = [
     "m3r_abi_version", "m3r_last_error", "m3r_iter_proj", "m3r_refine_matches_f16",
-    "m3r_refine_matches_f32", "m3r_refine_matches_f64", "m3r_gn_workspace_bytes", "m3r_gauss_newton",
-    "m3r_gn_prepare", "m3r_gn_accumulate", "m3r_gn_edge_blocks", "m3r_gn_solve_retract",
+    "m3r_refine_matches_f32", "m3r_refine_matches_f64", "m3r_gn_workspace_bytes", "m3r_gn_workspace_bytes_sharded",
+    "m3r_gauss_newton", "m3r_gn_prepare", "m3r_gn_pack", "m3r_gn_accumulate", "m3r_gn_edge_blocks", "m3r_gn_solve_retract",
     "m3r_gn_export_hs_gs", "m3r_pose_retr", "m3r_comm_unique_id", "m3r_comm_init", "m3r_comm_destroy",
     "m3r_comm_allreduce_f64",
 ]
@@ -47,6 +47,8 @@ def _load():
     lib.m3r_last_error.restype = C.c_char_p
     lib.m3r_gn_workspace_bytes.restype = C.c_size_t
     lib.m3r_gn_workspace_bytes.argtypes = [C.c_int, C.c_int, C.c_int]
+    lib.m3r_gn_workspace_bytes_sharded.restype = C.c_size_t
+    lib.m3r_gn_workspace_bytes_sharded.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int]
     return lib
 
 
@@ -107,8 +109,14 @@ def refine_matches(D11, D21, p1, radius, dilation_max):
     return [out]
 
 
-def gn_workspace(num_kf, num_edges, num_pts, device):
-    nbytes = lib.m3r_gn_workspace_bytes(num_kf, num_edges, num_pts)
+def gn_workspace(num_kf, num_edges, num_pts, device, edges_local=None):
+    """device workspace; a rank that owns only `edges_local` edges keeps packed slabs for those only"""
+    if edges_local is None:
+        nbytes = lib.m3r_gn_workspace_bytes(num_kf, num_edges, num_pts)
+    else:
+        nbytes = lib.m3r_gn_workspace_bytes_sharded(num_kf, num_edges, num_pts, int(edges_local))
+    if nbytes == 0:
+        raise M3RError("m3r_gn_workspace_bytes: bad problem size")
     return torch.empty(nbytes, dtype=torch.uint8, device=device), nbytes
 
 
@@ -150,12 +158,26 @@ def gn_prepare(ii, jj, num_kf, num_pts, workspace):
                               C.c_size_t(workspace.numel()), _stream()), "m3r_gn_prepare")
 
 
-def gn_accumulate(params, Twc, Xs, Cs, K, idx, valid, Q, num_edges, workspace, shard=None):
+def gn_pack(params, Cs, idx, valid, Q, num_kf, num_edges, workspace, shard=None):
+    """fold the pose-independent per-point data into the 8-byte records (once per problem)"""
+    n = Cs.shape[1]
+    sh = C.byref(shard) if shard is not None else None
+    _check(lib.m3r_gn_pack(_ptr(Cs), _ptr(idx), _ptr(valid), _ptr(Q), num_kf, n, num_edges, C.byref(params),
+                           _ptr(workspace), C.c_size_t(workspace.numel()), sh, _stream()), "m3r_gn_pack")
+
+
+def gn_accumulate_packed(params, Twc, Xs, K, num_edges, workspace, shard=None):
     N, n = Xs.shape[0], Xs.shape[1]
     sh = C.byref(shard) if shard is not None else None
-    _check(lib.m3r_gn_accumulate(_ptr(Twc), _ptr(Xs), _ptr(Cs), _ptr(K), _ptr(idx), _ptr(valid), _ptr(Q),
-                                 N, n, num_edges, C.byref(params), _ptr(workspace),
-                                 C.c_size_t(workspace.numel()), sh, _stream()), "m3r_gn_accumulate")
+    _check(lib.m3r_gn_accumulate(_ptr(Twc), _ptr(Xs), _ptr(K), N, n, num_edges, C.byref(params),
+                                 _ptr(workspace), C.c_size_t(workspace.numel()), sh, _stream()),
+           "m3r_gn_accumulate")
+
+
+def gn_accumulate(params, Twc, Xs, Cs, K, idx, valid, Q, num_edges, workspace, shard=None):
+    """pack + accumulate (the two building blocks of one GN iteration before the solve)"""
+    gn_pack(params, Cs, idx, valid, Q, Xs.shape[0], num_edges, workspace, shard)
+    gn_accumulate_packed(params, Twc, Xs, K, num_edges, workspace, shard)
 
 
 def gn_export_hs_gs(workspace, num_kf, num_edges, num_pts):

@@ -10,16 +10,25 @@
 //    Jacobian row removed at compile time).  The reference accumulates 105 + 14 terms per point in
 //    local memory and applies the adjoint per point (~1.5 kflop/pt); here it is ~0.2 kflop/pt and
 //    the adjoint is applied once per edge in fp64: A_e = G^T M G, b_e = G^T v.
-//  * the grid is (point-chunks x edges), not one CTA per edge, so a 2-edge tracking problem still
-//    fills the 148 SMs; each thread streams 4 consecutive points per step with 16-byte loads
-//    (idx as 2x longlong2, Xs[j] as 3x float4, Q / Cs[j] as float4, valid as uchar4).
+//  * everything that does not depend on the poses is folded ONCE per solve by gn_pack_kernel into an
+//    8-byte record per (edge, point): {int32 m, float sqrt(Q)} with m = -1 when
+//    !(valid_match && Q > Q_thresh && C_i[m] > C_thresh && C_j[k] > C_thresh).  The max_iter
+//    iterations then stream 8 B/pt/edge instead of 13 B + two confidence reads, and never touch Cs.
+//  * the grid is (point-chunks x edges).  A CTA stages its chunk of the two contiguous streams
+//    (packed records, Xs[j]) through shared memory with TMA bulk copies (cp.async.bulk + mbarrier),
+//    all tiles issued up-front, so the only long-latency accesses left in the loop are the Xs[i][m]
+//    gathers, issued for all of a thread's points of the tile before any arithmetic.  Consecutive
+//    CTAs work on the same edge and the two directions of a keyframe pair are adjacent in the edge
+//    list, so Xs[i] / Xs[j] are served by the L2 after their first touch.
 //  * reduction: warp shuffles -> shared memory -> one fp64 partial per CTA, then the LAST CTA of
 //    an edge (ticket counter) sums the partials in a fixed order, applies the adjoint and writes
 //    the edge block EB[e] = {A_e (7x7), b_e (7)} in fp64.  Per-pixel Jacobians never touch HBM and
 //    the result is bit-reproducible from run to run (no floating-point atomics).
+//  * small systems (tracking): the last CTA of the last edge also assembles, factors and solves the
+//    system and retracts the poses (gn_device.cuh: small_solve), i.e. ONE launch per GN iteration.
 //
 // H_ii = H_jj = A_e, H_ij = H_ji = -A_e, g_i = -b_e, g_j = +b_e (gn_kernels.cu:1096-1137).
-#include "gn_common.cuh"
+#include "gn_device.cuh"
 
 namespace m3r {
 namespace {
@@ -67,24 +76,14 @@ struct AccumParams {
 
 template <int KIND>
 __device__ __forceinline__ void accum_point(float (&acc)[kAcc], const EdgeXform& X, const AccumParams& prm,
-                                            float xjx, float xjy, float xjz, float cj, float q, bool vm,
-                                            long long m, const float* __restrict__ Xi_base,
-                                            const float* __restrict__ Ci_base) {
-  // gather the matched point of frame i (index 0 for an invalid match, like the reference :914)
-  const long long mi = vm ? m : 0;
-  const float xix = __ldg(Xi_base + mi * 3 + 0);
-  const float xiy = __ldg(Xi_base + mi * 3 + 1);
-  const float xiz = __ldg(Xi_base + mi * 3 + 2);
-  const float ci = __ldg(Ci_base + mi);
-  bool ok = vm & (q > prm.Q_thresh) & (ci > prm.C_thresh) & (cj > prm.C_thresh);
-
+                                            float xjx, float xjy, float xjz, float sq, int mi,
+                                            float xix, float xiy, float xiz) {
+  bool ok = true;
   const float px = fmaf(X.m[0], xjx, fmaf(X.m[1], xjy, fmaf(X.m[2], xjz, X.t[0])));
   const float py = fmaf(X.m[3], xjx, fmaf(X.m[4], xjy, fmaf(X.m[5], xjz, X.t[1])));
   const float pz = fmaf(X.m[6], xjx, fmaf(X.m[7], xjy, fmaf(X.m[8], xjz, X.t[2])));
-  const float sq = sqrtf(q);
 
   if (KIND == M3R_GN_POINTS) {
-    if (!ok) return;
     const float sw = prm.inv_sigma_a * sq;
     const float wc = sw * sw;
     const float e0 = px - xix, e1 = py - xiy, e2 = pz - xiz;
@@ -101,7 +100,6 @@ __device__ __forceinline__ void accum_point(float (&acc)[kAcc], const EdgeXform&
       rank1<0x5Cu>(acc, J, huber(sw * e2) * wc, e2);
     }
   } else if (KIND == M3R_GN_RAYS) {
-    if (!ok) return;
     const float n2j = fmaf(px, px, fmaf(py, py, pz * pz));
     const float inv_j = rsqrtf(n2j);
     const float rho = n2j * inv_j;
@@ -139,8 +137,7 @@ __device__ __forceinline__ void accum_point(float (&acc)[kAcc], const EdgeXform&
     const float u = fmaf(prm.fx, xz_, prm.cx), v = fmaf(prm.fy, yz_, prm.cy);
     ok = ok & vz & (u > prm.u_lo) & (u < prm.u_hi) & (v > prm.v_lo) & (v < prm.v_hi);
     if (!ok) return;
-    const int mi32 = static_cast<int>(mi);
-    const int ut = mi32 % prm.width, vt = mi32 / prm.width;
+    const int ut = mi % prm.width, vt = mi / prm.width;
     const float e0 = u - static_cast<float>(ut), e1 = v - static_cast<float>(vt);
     const float e2 = logf(pz) - logf(xiz);
     const float swp = prm.inv_sigma_a * sq, swd = prm.inv_sigma_b * sq;
@@ -165,20 +162,59 @@ __device__ __forceinline__ void accum_point(float (&acc)[kAcc], const EdgeXform&
 struct AccumArgs {
   const float* Twc;
   const float* Xs;
-  const float* Cs;
   const float* K;
-  const int64_t* idx;   // local slabs [E_local, n]
-  const uint8_t* valid;
-  const float* Q;
+  const uint2* packed;  // local slabs [E_local, n]: {int32 m | -1, float sqrt(Q)}
   const int* ci;
   const int* cj;
   const int* ctrl;
-  unsigned* counters;
+  const int* order;     // launch slot -> local edge (NULL: identity); see gn_prepare_kernel
+  unsigned* counters;   // [E] per-edge tickets, [E] (last word) = edges done in this launch
   double* partials;
   double* eb;
-  int n, e_lo, chunks, groups_per_chunk;  // group = VEC points
+  int n, e_lo, e_local, chunks, chunk_pts, tile_pts;
   AccumParams prm;
+  int ss_counter;       // index in counters of the "edges done" ticket
+  int fuse;             // 1: the last CTA of the launch solves + retracts (small systems)
+  SmallSolveArgs ss;
 };
+
+// ---- TMA bulk copy + mbarrier (PTX; SASS: UBLKCP / SYNCS) --------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t phase) {
+  uint32_t done = 0;
+  while (!done) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(phase)
+        : "memory");
+  }
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+// global -> shared bulk copy; bytes % 16 == 0, both addresses 16-byte aligned
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar, uint64_t pol) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+      ::"r"(dst), "l"(src), "r"(bytes), "r"(bar), "l"(pol)
+      : "memory");
+}
 
 // relative pose T_ij = T_i^-1 T_j in fp64 -> fp32 3x4
 __device__ __forceinline__ void edge_xform(const float* __restrict__ Ti, const float* __restrict__ Tj, EdgeXform& X) {
@@ -208,15 +244,102 @@ __device__ __forceinline__ void edge_xform(const float* __restrict__ Ti, const f
   X.t[2] = (float)((Ri[6] * dx + Ri[7] * dy + Ri[8] * dz) * si_inv);
 }
 
-template <int KIND, int VEC>
-__global__ void __launch_bounds__(kAccumThreads)
+// ---- pose-independent fold: {idx, valid, Q, C_i[m], C_j[k]} -> 8-byte record, once per solve ----
+struct PackArgs {
+  const float* Cs;
+  const int64_t* idx;   // local slabs [E_local, n]
+  const uint8_t* valid;
+  const float* Q;
+  const int* ci;
+  const int* cj;
+  uint2* packed;
+  int n, e_lo;
+  float C_thresh, Q_thresh;
+};
+
+__device__ __forceinline__ uint2 pack_one(long long m, bool vm, float q, float cj, const float* __restrict__ Ci,
+                                          float C_thresh, float Q_thresh) {
+  // invalid matches read C_i[0] in the reference (gn_kernels.cu:913-914); the result is discarded
+  const float ci = __ldg(Ci + (vm ? m : 0));
+  const bool ok = vm & (q > Q_thresh) & (ci > C_thresh) & (cj > C_thresh);
+  return make_uint2(ok ? (unsigned)(int)m : 0xffffffffu, __float_as_uint(sqrtf(q)));
+}
+
+template <int VEC>
+__global__ void __launch_bounds__(256)
+gn_pack_kernel(const PackArgs a) {
+  const int el = blockIdx.y;
+  const int e = a.e_lo + el;
+  const int n = a.n;
+  const float* __restrict__ Ci = a.Cs + (size_t)a.ci[e] * n;
+  const float* __restrict__ Cj = a.Cs + (size_t)a.cj[e] * n;
+  const int64_t* __restrict__ idx = a.idx + (size_t)el * n;
+  const uint8_t* __restrict__ valid = a.valid + (size_t)el * n;
+  const float* __restrict__ Q = a.Q + (size_t)el * n;
+  uint2* __restrict__ out = a.packed + (size_t)el * n;
+  const size_t k0 = ((size_t)blockIdx.x * 256 + threadIdx.x) * VEC;
+  if (k0 >= (size_t)n) return;
+  if (VEC == 4) {
+    const uchar4 vm = __ldcs(reinterpret_cast<const uchar4*>(valid + k0));
+    const longlong2 m01 = __ldcs(reinterpret_cast<const longlong2*>(idx + k0));
+    const longlong2 m23 = __ldcs(reinterpret_cast<const longlong2*>(idx + k0) + 1);
+    const float4 q4 = __ldcs(reinterpret_cast<const float4*>(Q + k0));
+    const float4 c4 = __ldg(reinterpret_cast<const float4*>(Cj + k0));
+    const uint2 r0 = pack_one(m01.x, vm.x != 0, q4.x, c4.x, Ci, a.C_thresh, a.Q_thresh);
+    const uint2 r1 = pack_one(m01.y, vm.y != 0, q4.y, c4.y, Ci, a.C_thresh, a.Q_thresh);
+    const uint2 r2 = pack_one(m23.x, vm.z != 0, q4.z, c4.z, Ci, a.C_thresh, a.Q_thresh);
+    const uint2 r3 = pack_one(m23.y, vm.w != 0, q4.w, c4.w, Ci, a.C_thresh, a.Q_thresh);
+    reinterpret_cast<uint4*>(out + k0)[0] = make_uint4(r0.x, r0.y, r1.x, r1.y);
+    reinterpret_cast<uint4*>(out + k0)[1] = make_uint4(r2.x, r2.y, r3.x, r3.y);
+  } else {
+    out[k0] = pack_one(idx[k0], valid[k0] != 0, Q[k0], __ldg(Cj + k0), Ci, a.C_thresh, a.Q_thresh);
+  }
+}
+
+template <int KIND, bool STAGED>
+__global__ void __launch_bounds__(kAccumThreads, 2)
 gn_accum_kernel(const AccumArgs a) {
   if (a.ctrl[CTRL_DONE]) return;
-  const int el = blockIdx.y;          // local edge
-  const int e = a.e_lo + el;          // global edge
+  extern __shared__ __align__(128) unsigned char dsm[];
+  __shared__ __align__(8) unsigned long long s_bar[kStages];
+  const int tid = threadIdx.x;
+  const int el = a.order ? a.order[blockIdx.y] : blockIdx.y;  // local edge
+  const int e = a.e_lo + el;                                   // global edge
   const int chunk = blockIdx.x;
   const int i = a.ci[e], j = a.cj[e];
   const int n = a.n;
+  const int tile = a.tile_pts;
+  const int p_lo = chunk * a.chunk_pts;
+  const int p_hi = min(n, p_lo + a.chunk_pts);
+  // a self-edge contributes nothing (H_ii + H_jj - H_ij - H_ji = 0)
+  const int ntiles = (i != j && p_hi > p_lo) ? (p_hi - p_lo + tile - 1) / tile : 0;
+
+  const float* __restrict__ Xi = a.Xs + (size_t)i * n * 3;
+  const float* __restrict__ Xj = a.Xs + (size_t)j * n * 3;
+  const uint2* __restrict__ gpk = a.packed + (size_t)el * n;
+  const uint32_t stage_bytes = (uint32_t)tile * 20u;
+
+  if (STAGED) {
+    if (tid == 0) {
+#pragma unroll
+      for (int s = 0; s < kStages; s++) mbar_init(smem_u32(&s_bar[s]), 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (tid == 0) {
+      const uint64_t pol_stream = l2_policy_evict_first();  // records are read once per iteration
+      const uint64_t pol_keep = l2_policy_evict_last();     // Xs[j] is re-read by the other edges of j
+      for (int s = 0; s < ntiles; s++) {
+        const int t_lo = p_lo + s * tile;
+        const uint32_t cnt = (uint32_t)min(tile, p_hi - t_lo);
+        const uint32_t bar = smem_u32(&s_bar[s]);
+        const uint32_t dst = smem_u32(dsm) + (uint32_t)s * stage_bytes;
+        mbar_expect_tx(bar, cnt * 20u);
+        bulk_g2s(dst, gpk + t_lo, cnt * 8u, bar, pol_stream);
+        bulk_g2s(dst + (uint32_t)tile * 8u, Xj + (size_t)t_lo * 3, cnt * 12u, bar, pol_keep);
+      }
+    }
+  }
 
   EdgeXform X;
   edge_xform(a.Twc + (size_t)i * 8, a.Twc + (size_t)j * 8, X);
@@ -228,53 +351,59 @@ gn_accum_kernel(const AccumArgs a) {
     prm.cy = __ldg(a.K + 5);
   }
 
-  const float* __restrict__ Xi = a.Xs + (size_t)i * n * 3;
-  const float* __restrict__ Ci = a.Cs + (size_t)i * n;
-  const float* __restrict__ Xj = a.Xs + (size_t)j * n * 3;
-  const float* __restrict__ Cj = a.Cs + (size_t)j * n;
-  const int64_t* __restrict__ idx = a.idx + (size_t)el * n;
-  const uint8_t* __restrict__ valid = a.valid + (size_t)el * n;
-  const float* __restrict__ Q = a.Q + (size_t)el * n;
-
   float acc[kAcc];
 #pragma unroll
   for (int t = 0; t < kAcc; t++) acc[t] = 0.f;
 
-  const int total_groups = (n + VEC - 1) / VEC;
-  const int g_lo = chunk * a.groups_per_chunk;
-  int g_hi = g_lo + a.groups_per_chunk;
-  if (g_hi > total_groups) g_hi = total_groups;
-
-  if (i != j) {
-    for (int g = g_lo + threadIdx.x; g < g_hi; g += kAccumThreads) {
-      if (VEC == 4) {
-        const size_t k0 = (size_t)g * 4;
-        const uchar4 vm = __ldg(reinterpret_cast<const uchar4*>(valid + k0));
-        const longlong2 m01 = __ldg(reinterpret_cast<const longlong2*>(idx + k0));
-        const longlong2 m23 = __ldg(reinterpret_cast<const longlong2*>(idx + k0) + 1);
-        const float4 q4 = __ldg(reinterpret_cast<const float4*>(Q + k0));
-        const float4 c4 = __ldg(reinterpret_cast<const float4*>(Cj + k0));
-        const float4 xa = __ldg(reinterpret_cast<const float4*>(Xj + k0 * 3));
-        const float4 xb = __ldg(reinterpret_cast<const float4*>(Xj + k0 * 3) + 1);
-        const float4 xc = __ldg(reinterpret_cast<const float4*>(Xj + k0 * 3) + 2);
-        accum_point<KIND>(acc, X, prm, xa.x, xa.y, xa.z, c4.x, q4.x, vm.x != 0, m01.x, Xi, Ci);
-        accum_point<KIND>(acc, X, prm, xa.w, xb.x, xb.y, c4.y, q4.y, vm.y != 0, m01.y, Xi, Ci);
-        accum_point<KIND>(acc, X, prm, xb.z, xb.w, xc.x, c4.z, q4.z, vm.z != 0, m23.x, Xi, Ci);
-        accum_point<KIND>(acc, X, prm, xc.y, xc.z, xc.w, c4.w, q4.w, vm.w != 0, m23.y, Xi, Ci);
-      } else {
-        const size_t k0 = (size_t)g;
-        accum_point<KIND>(acc, X, prm, __ldg(Xj + k0 * 3), __ldg(Xj + k0 * 3 + 1), __ldg(Xj + k0 * 3 + 2),
-                          __ldg(Cj + k0), __ldg(Q + k0), valid[k0] != 0, idx[k0], Xi, Ci);
+  for (int s = 0; s < ntiles; s++) {
+    const int t_lo = p_lo + s * tile;
+    const int cnt = min(tile, p_hi - t_lo);
+    const uint2* spk;
+    const float* sx;
+    if (STAGED) {
+      mbar_wait(smem_u32(&s_bar[s]), 0);
+      spk = reinterpret_cast<const uint2*>(dsm + (size_t)s * stage_bytes);
+      sx = reinterpret_cast<const float*>(dsm + (size_t)s * stage_bytes + (size_t)tile * 8);
+    } else {
+      spk = gpk + t_lo;
+      sx = Xj + (size_t)t_lo * 3;
+    }
+    for (int k0 = tid; k0 < cnt; k0 += 4 * kAccumThreads) {
+      int m[4];
+      float sq[4], xi[4][3];
+#pragma unroll
+      for (int r = 0; r < 4; r++) {
+        const int k = k0 + r * kAccumThreads;
+        uint2 rec = make_uint2(0xffffffffu, 0u);
+        if (k < cnt) rec = spk[k];
+        m[r] = (int)rec.x;
+        sq[r] = __uint_as_float(rec.y);
+      }
+      // all gathers of this pass are in flight before any arithmetic (record 0 for masked points)
+#pragma unroll
+      for (int r = 0; r < 4; r++) {
+        const float* g = Xi + (size_t)max(m[r], 0) * 3;
+        xi[r][0] = __ldg(g + 0);
+        xi[r][1] = __ldg(g + 1);
+        xi[r][2] = __ldg(g + 2);
+      }
+#pragma unroll
+      for (int r = 0; r < 4; r++) {
+        if (m[r] >= 0) {
+          const float* xj = sx + (size_t)(k0 + r * kAccumThreads) * 3;
+          accum_point<KIND>(acc, X, prm, xj[0], xj[1], xj[2], sq[r], m[r], xi[r][0], xi[r][1], xi[r][2]);
+        }
       }
     }
   }
-
   // ---- CTA reduction: shuffles -> smem -> fp64 partial ----
   __shared__ float s_warp[kAccumThreads / 32][kAcc];
+  __shared__ double s_part[7][kAcc];
   __shared__ double s_mv[kAcc];
   __shared__ double s_G[49];
+  __shared__ double s_T[56];
   __shared__ bool s_last;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int lane = tid & 31, warp = tid >> 5;
 #pragma unroll
   for (int t = 0; t < kAcc; t++) {
     float v = acc[t];
@@ -283,17 +412,19 @@ gn_accum_kernel(const AccumArgs a) {
     if (lane == 0) s_warp[warp][t] = v;
   }
   __syncthreads();
-  double* part = a.partials + ((size_t)el * a.chunks + chunk) * kAcc;
-  if (threadIdx.x < kAcc) {
+  if (tid < kAcc) {
     double s = 0.0;
 #pragma unroll
-    for (int wv = 0; wv < kAccumThreads / 32; wv++) s += (double)s_warp[wv][threadIdx.x];
-    part[threadIdx.x] = s;
+    for (int wv = 0; wv < kAccumThreads / 32; wv++) s += (double)s_warp[wv][tid];
+    if (a.chunks > 1)
+      a.partials[((size_t)el * a.chunks + chunk) * kAcc + tid] = s;
+    else
+      s_mv[tid] = s;
   }
   if (a.chunks > 1) {
     __threadfence();
     __syncthreads();
-    if (threadIdx.x == 0) {
+    if (tid == 0) {
       const unsigned ticket = atomicAdd(a.counters + e, 1u);
       s_last = (ticket == (unsigned)a.chunks - 1u);
       if (s_last) a.counters[e] = 0;  // re-arm for the next iteration
@@ -301,18 +432,27 @@ gn_accum_kernel(const AccumArgs a) {
     __syncthreads();
     if (!s_last) return;
     __threadfence();
+    // last CTA of the edge: fixed-order fp64 sum of the partials (7 interleaved slices, then 7 -> 1)
+    if (tid < 7 * kAcc) {
+      const int t = tid % kAcc, sl = tid / kAcc;
+      const double* p0 = a.partials + (size_t)el * a.chunks * kAcc + t;
+      double s = 0.0;
+      for (int c = sl; c < a.chunks; c += 7) s += __ldcg(p0 + (size_t)c * kAcc);
+      s_part[sl][t] = s;
+    }
+    __syncthreads();
+    if (tid < kAcc) {
+      double s = s_part[0][tid];
+#pragma unroll
+      for (int sl = 1; sl < 7; sl++) s += s_part[sl][tid];
+      s_mv[tid] = s;
+    }
   }
 
-  // ---- last CTA of the edge: fixed-order fp64 sum, adjoint, edge block ----
-  if (threadIdx.x < kAcc) {
-    const double* p0 = a.partials + (size_t)el * a.chunks * kAcc + threadIdx.x;
-    double s = 0.0;
-    for (int c = 0; c < a.chunks; c++) s += __ldcg(p0 + (size_t)c * kAcc);
-    s_mv[threadIdx.x] = s;
-  }
-  if (threadIdx.x >= 64 && threadIdx.x < 64 + 7) {
+  // ---- adjoint: A_e = G^T M G, b_e = G^T v in fp64 ----
+  if (tid >= 64 && tid < 64 + 7) {
     // G: Y = X * G is the row-vector adjoint of gn_kernels.cu:277-297 for pose i; row m = image of e_m
-    const int m = threadIdx.x - 64;
+    const int m = tid - 64;
     const float* Ti = a.Twc + (size_t)i * 8;
     const double tx = Ti[0], ty = Ti[1], tz = Ti[2], x = Ti[3], y = Ti[4], z = Ti[5], w = Ti[6];
     const double s_inv = 1.0 / (double)Ti[7];
@@ -336,34 +476,64 @@ gn_accum_kernel(const AccumArgs a) {
     for (int c = 0; c < 7; c++) s_G[m * 7 + c] = row[c];
   }
   __syncthreads();
-  double* out = a.eb + (size_t)e * kEdgeBlock;
-  if (threadIdx.x < 49) {
-    const int r = threadIdx.x / 7, c = threadIdx.x % 7;
-    double s = 0.0;
-    for (int p = 0; p < 7; p++) {
-      double t = 0.0;
-      for (int q = 0; q < 7; q++) {
-        const double mpq = (p <= q) ? s_mv[tri(p, q)] : s_mv[tri(q, p)];
-        t += mpq * s_G[q * 7 + c];
-      }
-      s += s_G[p * 7 + r] * t;
-    }
-    out[threadIdx.x] = s;
-  } else if (threadIdx.x < 56) {
-    const int r = threadIdx.x - 49;
-    double s = 0.0;
-    for (int p = 0; p < 7; p++) s += s_G[p * 7 + r] * s_mv[28 + p];
-    out[threadIdx.x] = s;
+  if (tid < 49) {  // T = M G
+    const int p = tid / 7, c = tid % 7;
+    double t = 0.0;
+#pragma unroll
+    for (int q = 0; q < 7; q++) t += ((p <= q) ? s_mv[tri(p, q)] : s_mv[tri(q, p)]) * s_G[q * 7 + c];
+    s_T[tid] = t;
   }
+  __syncthreads();
+  double* out = a.eb + (size_t)e * kEdgeBlock;
+  if (tid < 49) {
+    const int r = tid / 7, c = tid % 7;
+    double s = 0.0;
+#pragma unroll
+    for (int p = 0; p < 7; p++) s += s_G[p * 7 + r] * s_T[p * 7 + c];
+    out[tid] = s;
+  } else if (tid < 56) {
+    const int r = tid - 49;
+    double s = 0.0;
+#pragma unroll
+    for (int p = 0; p < 7; p++) s += s_G[p * 7 + r] * s_mv[28 + p];
+    out[tid] = s;
+  }
+  if (!a.fuse) return;
+
+  // ---- fused small-system solve: the CTA that completes the LAST edge of the launch ----
+  if (a.e_local > 1) {
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+      unsigned* done = a.counters + a.ss_counter;
+      const unsigned ticket = atomicAdd(done, 1u);
+      s_last = (ticket == (unsigned)a.e_local - 1u);
+      if (s_last) *done = 0;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+  } else {
+    __threadfence();
+    __syncthreads();
+  }
+  small_solve(a.ss, reinterpret_cast<double*>(dsm));
 }
 
 template <int KIND>
-int launch_kind(const AccumArgs& a, int e_local, bool vec4, cudaStream_t s) {
-  dim3 grid(a.chunks, e_local);
-  if (vec4)
-    gn_accum_kernel<KIND, 4><<<grid, kAccumThreads, 0, s>>>(a);
-  else
-    gn_accum_kernel<KIND, 1><<<grid, kAccumThreads, 0, s>>>(a);
+int launch_kind(const AccumArgs& a, bool staged, size_t dyn, cudaStream_t s) {
+  dim3 grid(a.chunks, a.e_local);
+  if (staged) {
+    static bool attr_done = false;  // per kernel instantiation
+    if (!attr_done) {
+      M3R_CUDA_CHECK(cudaFuncSetAttribute(gn_accum_kernel<KIND, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          kStages * 1024 * 20));
+      attr_done = true;
+    }
+    gn_accum_kernel<KIND, true><<<grid, kAccumThreads, dyn, s>>>(a);
+  } else {
+    gn_accum_kernel<KIND, false><<<grid, kAccumThreads, dyn, s>>>(a);
+  }
   M3R_LAUNCH_CHECK();
   return M3R_OK;
 }
@@ -389,25 +559,44 @@ __global__ void export_hs_gs_kernel(const double* __restrict__ eb, int E, float*
 
 }  // namespace
 
-int launch_gn_accumulate(const float* Twc, const float* Xs, const float* Cs, const float* K,
-                         const int64_t* idx, const uint8_t* valid, const float* Q, const GnLayout& L,
-                         const GnPtrs& P, const m3r_gn_params& prm, int e_lo, int e_hi, cudaStream_t s) {
+int launch_gn_pack(const float* Cs, const int64_t* idx, const uint8_t* valid, const float* Q, const GnLayout& L,
+                   const GnPtrs& P, const m3r_gn_params& prm, int e_lo, int e_hi, cudaStream_t s) {
   const int e_local = e_hi - e_lo;
   if (e_local <= 0) return M3R_OK;
-  if (e_local > 65535) return M3R_ERR_UNSUPPORTED;
+  if (e_local > 65535 || e_local > L.edges_local) return M3R_ERR_UNSUPPORTED;
+  PackArgs a{};
+  a.Cs = Cs; a.idx = idx; a.valid = valid; a.Q = Q; a.ci = P.ci; a.cj = P.cj; a.packed = P.packed;
+  a.n = L.num_pts; a.e_lo = e_lo; a.C_thresh = prm.C_thresh; a.Q_thresh = prm.Q_thresh;
+  const bool vec4 = (L.num_pts % 4 == 0) &&
+                    ((reinterpret_cast<uintptr_t>(Cs) | reinterpret_cast<uintptr_t>(idx) |
+                      reinterpret_cast<uintptr_t>(Q) | reinterpret_cast<uintptr_t>(valid)) % 16 == 0);
+  if (vec4) {
+    dim3 grid((L.num_pts / 4 + 255) / 256, e_local);
+    gn_pack_kernel<4><<<grid, 256, 0, s>>>(a);
+  } else {
+    dim3 grid((L.num_pts + 255) / 256, e_local);
+    gn_pack_kernel<1><<<grid, 256, 0, s>>>(a);
+  }
+  M3R_LAUNCH_CHECK();
+  return M3R_OK;
+}
+
+int launch_gn_accumulate(const float* Twc, const float* Xs, const float* K, const GnLayout& L, const GnPtrs& P,
+                         const m3r_gn_params& prm, int e_lo, int e_hi, const GnFuse& fuse, cudaStream_t s) {
+  const int e_local = e_hi - e_lo;
+  if (e_local <= 0) return M3R_OK;
+  if (e_local > 65535 || e_local > L.edges_local) return M3R_ERR_UNSUPPORTED;
   AccumArgs a{};
-  a.Twc = Twc; a.Xs = Xs; a.Cs = Cs; a.K = K; a.idx = idx; a.valid = valid; a.Q = Q;
+  a.Twc = Twc; a.Xs = Xs; a.K = K; a.packed = P.packed;
   a.ci = P.ci; a.cj = P.cj; a.ctrl = P.ctrl; a.counters = P.counters; a.partials = P.partials; a.eb = P.eb;
   a.n = L.num_pts;
   a.e_lo = e_lo;
-  a.chunks = gn_chunks(e_local, L.num_pts);
-  const bool vec4 = (L.num_pts % 4 == 0) &&
-                    ((reinterpret_cast<uintptr_t>(Xs) | reinterpret_cast<uintptr_t>(Cs) |
-                      reinterpret_cast<uintptr_t>(idx) | reinterpret_cast<uintptr_t>(Q) |
-                      reinterpret_cast<uintptr_t>(valid)) % 16 == 0);
-  const int vec = vec4 ? 4 : 1;
-  const int total_groups = (L.num_pts + vec - 1) / vec;
-  a.groups_per_chunk = (total_groups + a.chunks - 1) / a.chunks;
+  a.e_local = e_local;
+  // chunking depends on the FULL edge count, so a shard's blocks are bit-identical to the unsharded run's
+  const GnChunking ck = gn_chunking(L.num_edges, L.num_pts);
+  a.chunks = ck.chunks; a.chunk_pts = ck.chunk_pts; a.tile_pts = ck.tile_pts;
+  a.ss_counter = L.num_edges;
+  a.order = (e_lo == 0 && e_hi == L.num_edges) ? P.order : nullptr;  // shards are pre-ordered by the host
   a.prm.inv_sigma_a = (float)(1.0 / (double)prm.sigma_a);
   a.prm.inv_sigma_b = prm.kind == M3R_GN_POINTS ? 0.f : (float)(1.0 / (double)prm.sigma_b);
   a.prm.C_thresh = prm.C_thresh;
@@ -418,13 +607,23 @@ int launch_gn_accumulate(const float* Twc, const float* Xs, const float* Cs, con
   a.prm.u_hi = (float)(prm.width - 1 - prm.pixel_border);
   a.prm.v_lo = (float)prm.pixel_border;
   a.prm.v_hi = (float)(prm.height - 1 - prm.pixel_border);
-  if (prm.kind == M3R_GN_CALIB) {
-    if (!K) return M3R_ERR_BAD_ARG;  // read on the device by the kernel: the call stays asynchronous
+  if (prm.kind == M3R_GN_CALIB && !K) return M3R_ERR_BAD_ARG;  // read on the device: the call stays asynchronous
+  // TMA bulk copies need 16-byte aligned sources and sizes: n % 4 == 0 makes every tile of both streams so
+  const bool staged = (L.num_pts % 4 == 0) && (reinterpret_cast<uintptr_t>(Xs) % 16 == 0);
+  size_t dyn = staged ? (size_t)kStages * ck.tile_pts * 20 : 0;
+  a.fuse = 0;
+  if (fuse.enabled && L.dim <= kSmallDim && e_lo == 0 && e_hi == L.num_edges) {
+    a.fuse = 1;
+    a.ss.Twc = fuse.Twc; a.ss.eb = P.eb; a.ss.ci = P.ci; a.ss.cj = P.cj; a.ss.inc_off = P.inc_off;
+    a.ss.inc_list = P.inc_list; a.ss.ctrl = P.ctrl; a.ss.dx_out = fuse.dx_out; a.ss.info_out = fuse.info_out;
+    a.ss.N = L.num_kf; a.ss.dim = L.dim; a.ss.delta_thresh = fuse.delta_thresh;
+    const size_t need = small_solve_smem_bytes(L.dim);
+    if (need > dyn) dyn = need;
   }
   switch (prm.kind) {
-    case M3R_GN_POINTS: return launch_kind<M3R_GN_POINTS>(a, e_local, vec4, s);
-    case M3R_GN_RAYS: return launch_kind<M3R_GN_RAYS>(a, e_local, vec4, s);
-    case M3R_GN_CALIB: return launch_kind<M3R_GN_CALIB>(a, e_local, vec4, s);
+    case M3R_GN_POINTS: return launch_kind<M3R_GN_POINTS>(a, staged, dyn, s);
+    case M3R_GN_RAYS: return launch_kind<M3R_GN_RAYS>(a, staged, dyn, s);
+    case M3R_GN_CALIB: return launch_kind<M3R_GN_CALIB>(a, staged, dyn, s);
     default: return M3R_ERR_BAD_ARG;
   }
 }

@@ -10,20 +10,30 @@ constexpr int kEdgeBlock = 56;  // per directed edge: A_e (49, row-major) + b_e 
 constexpr int kTile = 32;       // Cholesky tile
 constexpr int kAccumThreads = 256;
 constexpr int kSolveThreads = 256;
-constexpr int kMaxChunks = 256;
 
 // ctrl words (device int32)
 enum { CTRL_DONE = 0, CTRL_ITERS = 1, CTRL_FAILS = 2, CTRL_EARLY = 3, CTRL_BAD = 4, CTRL_FAIL_NOW = 5, CTRL_WORDS = 16 };
 
-// How many point-chunks (CTAs) each edge is split into.  Pure function of (E, n) so that the
-// workspace size and every launch agree.  Target: >= 8 CTAs per SM in flight overall.
-inline int gn_chunks(int num_edges_local, int n) {
-  const int want = (kNumSMs * 8 + num_edges_local - 1) / (num_edges_local > 0 ? num_edges_local : 1);
-  int max_chunks = (n + 1023) / 1024;
-  if (max_chunks < 1) max_chunks = 1;
-  int c = want < 1 ? 1 : want;
-  if (c > max_chunks) c = max_chunks;
-  if (c > kMaxChunks) c = kMaxChunks;
+// Point-chunking of one edge (pure function of (E_local, n) so that the workspace size and every
+// launch agree).  A CTA owns `chunk_pts` consecutive points of one edge, staged through shared
+// memory as up to kStages tiles of `tile_pts` points (TMA bulk copies, all issued up-front).
+//  * big graphs: 1024-point tiles, 4096-point chunks -> few edges in flight at a time, so both
+//    directions of a keyframe pair find Xs[i] / Xs[j] in the 126 MB L2;
+//  * small graphs (tracking: 2 edges): 256-point tiles so that there are >= 2 CTAs per SM.
+constexpr int kStages = 4;
+constexpr int kSmallDim = 63;   // systems up to 9 free poses are solved inside the accumulate kernel
+struct GnChunking {
+  int tile_pts, chunk_pts, chunks;
+};
+inline GnChunking gn_chunking(int num_edges_local, int n) {
+  GnChunking c;
+  c.tile_pts = 1024;
+  const long long e = num_edges_local > 0 ? num_edges_local : 1;
+  while (c.tile_pts > 256 && e * ((n + c.tile_pts * kStages - 1) / (c.tile_pts * kStages)) < 2LL * kNumSMs)
+    c.tile_pts >>= 1;
+  c.chunk_pts = c.tile_pts * kStages;
+  c.chunks = (n + c.chunk_pts - 1) / c.chunk_pts;
+  if (c.chunks < 1) c.chunks = 1;
   return c;
 }
 
@@ -31,10 +41,11 @@ struct GnLayout {
   int num_kf, num_edges, num_pts;
   int dim, nblk, ld, rows;  // system dim 7(N-1); tiles; leading dimension; rows incl. rhs tile row
   size_t off_ctrl, off_counters, off_ci, off_cj, off_bitmap, off_prefix, off_inc_off, off_inc_list,
-      off_partials, off_eb, off_hd, off_linv, off_total;
+      off_order, off_partials, off_eb, off_hd, off_linv, off_packed, off_total;
+  int edges_local;  // packed slabs are sized for this many edges (== num_edges unless sharded)
 };
 
-inline GnLayout gn_layout(int num_kf, int num_edges, int num_pts) {
+inline GnLayout gn_layout(int num_kf, int num_edges, int num_pts, int edges_local = -1) {
   GnLayout L{};
   L.num_kf = num_kf;
   L.num_edges = num_edges;
@@ -51,20 +62,23 @@ inline GnLayout gn_layout(int num_kf, int num_edges, int num_pts) {
     return r;
   };
   L.off_ctrl = take(sizeof(int) * CTRL_WORDS);
-  L.off_counters = take(sizeof(unsigned) * (size_t)num_edges);
+  L.off_counters = take(sizeof(unsigned) * ((size_t)num_edges + 1));  // per-edge tickets + [E] = edges done
   L.off_ci = take(sizeof(int) * (size_t)num_edges);
   L.off_cj = take(sizeof(int) * (size_t)num_edges);
   L.off_bitmap = take(sizeof(unsigned) * (M3R_MAX_KF_ID / 32));
   L.off_prefix = take(sizeof(unsigned) * (M3R_MAX_KF_ID / 32));
   L.off_inc_off = take(sizeof(int) * ((size_t)num_kf + 1));
   L.off_inc_list = take(sizeof(int) * 2 * (size_t)num_edges);
-  // chunks(el) * el <= kNumSMs*8 + el for el <= kNumSMs*8, and == el above it (chunks == 1)
-  size_t worst = (size_t)2 * kNumSMs * 8 + 256;
-  if ((size_t)num_edges > worst) worst = (size_t)num_edges;
+  L.off_order = take(sizeof(int) * (size_t)num_edges);
+  // e_local * chunks(e_local) is largest with the smallest tile: n / 1024 + 1 chunks per edge
+  const size_t worst = (size_t)num_edges * ((size_t)num_pts / (256 * kStages) + 1);
   L.off_partials = take(sizeof(double) * kAcc * worst);
   L.off_eb = take(sizeof(double) * kEdgeBlock * (size_t)num_edges);
   L.off_hd = take(sizeof(double) * (size_t)L.rows * L.ld);
   L.off_linv = take(sizeof(double) * (size_t)L.nblk * kTile * kTile);
+  // packed per-point records {int32 m | -1, float sqrt(Q)} of the locally owned edges (last region)
+  L.edges_local = edges_local < 0 ? num_edges : edges_local;
+  L.off_packed = take(sizeof(uint2) * (size_t)L.edges_local * (size_t)num_pts);
   L.off_total = o;
   return L;
 }
@@ -78,10 +92,12 @@ struct GnPtrs {
   unsigned* prefix;
   int* inc_off;
   int* inc_list;
+  int* order;  // launch order of the edges: both directions of a keyframe pair adjacent, pairs sorted
   double* partials;
   double* eb;
   double* hd;
   double* linv;
+  uint2* packed;
 };
 
 inline GnPtrs gn_ptrs(const GnLayout& L, void* ws) {
@@ -95,18 +111,30 @@ inline GnPtrs gn_ptrs(const GnLayout& L, void* ws) {
   p.prefix = reinterpret_cast<unsigned*>(b + L.off_prefix);
   p.inc_off = reinterpret_cast<int*>(b + L.off_inc_off);
   p.inc_list = reinterpret_cast<int*>(b + L.off_inc_list);
+  p.order = reinterpret_cast<int*>(b + L.off_order);
   p.partials = reinterpret_cast<double*>(b + L.off_partials);
   p.eb = reinterpret_cast<double*>(b + L.off_eb);
   p.hd = reinterpret_cast<double*>(b + L.off_hd);
   p.linv = reinterpret_cast<double*>(b + L.off_linv);
+  p.packed = reinterpret_cast<uint2*>(b + L.off_packed);
   return p;
 }
 
+// fused tail of the accumulate kernel (dim <= kSmallDim, no collective): solve + retract in the last CTA
+struct GnFuse {
+  float* Twc;        // written by the fused solve
+  float* dx_out;
+  int32_t* info_out;
+  float delta_thresh;
+  int enabled;
+};
+
 // entry points implemented in gn_accum.cu / gn_solve.cu (host launchers)
 int launch_gn_prepare(const int64_t* ii, const int64_t* jj, const GnLayout& L, const GnPtrs& P, cudaStream_t s);
-int launch_gn_accumulate(const float* Twc, const float* Xs, const float* Cs, const float* K,
-                         const int64_t* idx, const uint8_t* valid, const float* Q, const GnLayout& L,
-                         const GnPtrs& P, const m3r_gn_params& prm, int e_lo, int e_hi, cudaStream_t s);
+int launch_gn_pack(const float* Cs, const int64_t* idx, const uint8_t* valid, const float* Q, const GnLayout& L,
+                   const GnPtrs& P, const m3r_gn_params& prm, int e_lo, int e_hi, cudaStream_t s);
+int launch_gn_accumulate(const float* Twc, const float* Xs, const float* K, const GnLayout& L, const GnPtrs& P,
+                         const m3r_gn_params& prm, int e_lo, int e_hi, const GnFuse& fuse, cudaStream_t s);
 int launch_gn_solve(float* Twc, const GnLayout& L, const GnPtrs& P, float delta_thresh, float* dx_out,
                     int32_t* info_out, cudaStream_t s);
 int launch_export_hs_gs(const GnLayout& L, const GnPtrs& P, float* Hs, float* gs, cudaStream_t s);

@@ -73,11 +73,19 @@ int nccl_fail(const char* what, int rc) {
   return M3R_ERR_NCCL;
 }
 
-int check_common(int num_kf, int num_pts, int num_edges, const void* ws, size_t ws_bytes, GnLayout* L) {
+// the packed slabs (last workspace region) are sized for the edges this rank owns
+int check_common(int num_kf, int num_pts, int num_edges, const void* ws, size_t ws_bytes, GnLayout* L,
+                 const m3r_gn_shard* shard = nullptr, bool needs_packed = false) {
   if (num_kf < 2 || num_pts < 1 || num_edges < 1) return M3R_ERR_BAD_ARG;
   if (!ws || (reinterpret_cast<uintptr_t>(ws) & 255)) return M3R_ERR_WORKSPACE;
-  *L = gn_layout(num_kf, num_edges, num_pts);
-  if (ws_bytes < L->off_total) return M3R_ERR_WORKSPACE;
+  int e_local = num_edges;
+  if (shard) {
+    if (shard->edge_lo < 0 || shard->edge_hi > num_edges || shard->edge_lo > shard->edge_hi) return M3R_ERR_BAD_ARG;
+    e_local = shard->edge_hi - shard->edge_lo;
+  }
+  *L = gn_layout(num_kf, num_edges, num_pts, e_local);
+  // calls without shard information (prepare / solve / export) never touch the packed slabs
+  if (ws_bytes < (needs_packed ? L->off_total : L->off_packed)) return M3R_ERR_WORKSPACE;
   return M3R_OK;
 }
 
@@ -92,9 +100,9 @@ int shard_range(const m3r_gn_shard* shard, int num_edges, int* lo, int* hi) {
   return M3R_OK;
 }
 
-int accumulate_step(const float* Twc, const float* Xs, const float* Cs, const float* K, const int64_t* idx,
-                    const uint8_t* valid, const float* Q, const GnLayout& L, const GnPtrs& P,
-                    const m3r_gn_params& prm, const m3r_gn_shard* shard, int lo, int hi, cudaStream_t s) {
+int accumulate_step(const float* Twc, const float* Xs, const float* K, const GnLayout& L, const GnPtrs& P,
+                    const m3r_gn_params& prm, const m3r_gn_shard* shard, int lo, int hi, const GnFuse& fuse,
+                    cudaStream_t s) {
   if (shard && (lo > 0 || hi < L.num_edges)) {
     // non-owned slots must be exact zeros so that the sum all-reduce acts as an all-gather
     if (lo > 0) M3R_CUDA_CHECK(cudaMemsetAsync(P.eb, 0, sizeof(double) * kEdgeBlock * (size_t)lo, s));
@@ -102,7 +110,7 @@ int accumulate_step(const float* Twc, const float* Xs, const float* Cs, const fl
       M3R_CUDA_CHECK(cudaMemsetAsync(P.eb + (size_t)hi * kEdgeBlock, 0,
                                      sizeof(double) * kEdgeBlock * (size_t)(L.num_edges - hi), s));
   }
-  int rc = launch_gn_accumulate(Twc, Xs, Cs, K, idx, valid, Q, L, P, prm, lo, hi, s);
+  int rc = launch_gn_accumulate(Twc, Xs, K, L, P, prm, lo, hi, fuse, s);
   if (rc != M3R_OK) return rc;
   if (shard && shard->comm) {
     rc = m3r_comm_allreduce_f64(shard->comm, P.eb, (size_t)L.num_edges * kEdgeBlock, s);
@@ -123,6 +131,11 @@ extern "C" size_t m3r_gn_workspace_bytes(int num_kf, int num_edges, int num_pts)
   return gn_layout(num_kf, num_edges, num_pts).off_total;
 }
 
+extern "C" size_t m3r_gn_workspace_bytes_sharded(int num_kf, int num_edges, int num_pts, int edges_local) {
+  if (num_kf < 2 || num_edges < 1 || num_pts < 1 || edges_local < 0 || edges_local > num_edges) return 0;
+  return gn_layout(num_kf, num_edges, num_pts, edges_local).off_total;
+}
+
 extern "C" int m3r_gn_prepare(const int64_t* ii, const int64_t* jj, int num_kf, int num_pts, int num_edges,
                               void* workspace, size_t workspace_bytes, void* stream) {
   if (!ii || !jj) return M3R_ERR_BAD_ARG;
@@ -132,18 +145,32 @@ extern "C" int m3r_gn_prepare(const int64_t* ii, const int64_t* jj, int num_kf, 
   return launch_gn_prepare(ii, jj, L, gn_ptrs(L, workspace), static_cast<cudaStream_t>(stream));
 }
 
-extern "C" int m3r_gn_accumulate(const float* Twc, const float* Xs, const float* Cs, const float* K,
-                                 const int64_t* idx, const uint8_t* valid, const float* Q, int num_kf,
-                                 int num_pts, int num_edges, const m3r_gn_params* params, void* workspace,
-                                 size_t workspace_bytes, const m3r_gn_shard* shard, void* stream) {
-  if (!Twc || !Xs || !Cs || !idx || !valid || !Q || !params) return M3R_ERR_BAD_ARG;
+extern "C" int m3r_gn_pack(const float* Cs, const int64_t* idx, const uint8_t* valid, const float* Q, int num_kf,
+                          int num_pts, int num_edges, const m3r_gn_params* params, void* workspace,
+                          size_t workspace_bytes, const m3r_gn_shard* shard, void* stream) {
+  if (!Cs || !idx || !valid || !Q || !params) return M3R_ERR_BAD_ARG;
   GnLayout L;
-  int rc = check_common(num_kf, num_pts, num_edges, workspace, workspace_bytes, &L);
+  int rc = check_common(num_kf, num_pts, num_edges, workspace, workspace_bytes, &L, shard, true);
   if (rc != M3R_OK) return rc;
   int lo, hi;
   rc = shard_range(shard, num_edges, &lo, &hi);
   if (rc != M3R_OK) return rc;
-  return accumulate_step(Twc, Xs, Cs, K, idx, valid, Q, L, gn_ptrs(L, workspace), *params, shard, lo, hi,
+  return launch_gn_pack(Cs, idx, valid, Q, L, gn_ptrs(L, workspace), *params, lo, hi,
+                        static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int m3r_gn_accumulate(const float* Twc, const float* Xs, const float* K, int num_kf, int num_pts,
+                                 int num_edges, const m3r_gn_params* params, void* workspace,
+                                 size_t workspace_bytes, const m3r_gn_shard* shard, void* stream) {
+  if (!Twc || !Xs || !params) return M3R_ERR_BAD_ARG;
+  GnLayout L;
+  int rc = check_common(num_kf, num_pts, num_edges, workspace, workspace_bytes, &L, shard, true);
+  if (rc != M3R_OK) return rc;
+  int lo, hi;
+  rc = shard_range(shard, num_edges, &lo, &hi);
+  if (rc != M3R_OK) return rc;
+  GnFuse nofuse{};
+  return accumulate_step(Twc, Xs, K, L, gn_ptrs(L, workspace), *params, shard, lo, hi, nofuse,
                          static_cast<cudaStream_t>(stream));
 }
 
@@ -187,22 +214,32 @@ extern "C" int m3r_gauss_newton(float* Twc, const float* Xs, const float* Cs, co
   if (params->kind == M3R_GN_CALIB && !K) return M3R_ERR_BAD_ARG;
   if (params->max_iter < 0) return M3R_ERR_BAD_ARG;
   GnLayout L;
-  int rc = check_common(num_kf, num_pts, num_edges, workspace, workspace_bytes, &L);
+  int rc = check_common(num_kf, num_pts, num_edges, workspace, workspace_bytes, &L, shard, true);
   if (rc != M3R_OK) return rc;
   int lo, hi;
   rc = shard_range(shard, num_edges, &lo, &hi);
   if (rc != M3R_OK) return rc;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   GnPtrs P = gn_ptrs(L, workspace);
+  // small systems without a collective: solve + retract ride in the accumulate kernel (1 launch / iteration)
+  GnFuse fuse{};
+  fuse.Twc = Twc; fuse.dx_out = dx_out; fuse.info_out = info_out; fuse.delta_thresh = params->delta_thresh;
+  fuse.enabled = (L.dim <= kSmallDim) && !(shard && shard->comm) && lo == 0 && hi == num_edges;
   M3R_CUDA_CHECK(cudaMemsetAsync(dx_out, 0, sizeof(float) * kPose * (size_t)(num_kf - 1), s));
   if (info_out) M3R_CUDA_CHECK(cudaMemsetAsync(info_out, 0, sizeof(int32_t) * 4, s));
   rc = launch_gn_prepare(ii, jj, L, P, s);
   if (rc != M3R_OK) return rc;
+  if (params->max_iter > 0) {
+    rc = launch_gn_pack(Cs, idx, valid, Q, L, P, *params, lo, hi, s);
+    if (rc != M3R_OK) return rc;
+  }
   for (int it = 0; it < params->max_iter; it++) {
-    rc = accumulate_step(Twc, Xs, Cs, K, idx, valid, Q, L, P, *params, shard, lo, hi, s);
+    rc = accumulate_step(Twc, Xs, K, L, P, *params, shard, lo, hi, fuse, s);
     if (rc != M3R_OK) return rc;
-    rc = launch_gn_solve(Twc, L, P, params->delta_thresh, dx_out, info_out, s);
-    if (rc != M3R_OK) return rc;
+    if (!fuse.enabled) {
+      rc = launch_gn_solve(Twc, L, P, params->delta_thresh, dx_out, info_out, s);
+      if (rc != M3R_OK) return rc;
+    }
   }
   return M3R_OK;
 }

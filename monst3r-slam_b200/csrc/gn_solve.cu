@@ -21,7 +21,7 @@
 //      following :299-413, ||dx|| stop test, next-iteration bookkeeping.
 #include <cooperative_groups.h>
 
-#include "gn_common.cuh"
+#include "gn_device.cuh"
 
 namespace cg = cooperative_groups;
 
@@ -34,14 +34,14 @@ __global__ void __launch_bounds__(1024)
 gn_prepare_kernel(const int64_t* __restrict__ ii, const int64_t* __restrict__ jj, int E, int N,
                   int* __restrict__ ci, int* __restrict__ cj, unsigned* __restrict__ bitmap,
                   unsigned* __restrict__ prefix, int* __restrict__ inc_off, int* __restrict__ inc_list,
-                  unsigned* __restrict__ counters, int* __restrict__ ctrl) {
+                  int* __restrict__ order, unsigned* __restrict__ counters, int* __restrict__ ctrl) {
   constexpr int W = M3R_MAX_KF_ID / 32;
   const int tid = threadIdx.x, nt = blockDim.x;
   __shared__ unsigned s_scan[1024];
   __shared__ int s_bad;
   if (tid == 0) s_bad = 0;
   for (int k = tid; k < W; k += nt) bitmap[k] = 0u;
-  for (int k = tid; k < E; k += nt) counters[k] = 0u;
+  for (int k = tid; k <= E; k += nt) counters[k] = 0u;
   if (tid < CTRL_WORDS) ctrl[tid] = 0;
   __syncthreads();
   for (int k = tid; k < 2 * E; k += nt) {
@@ -84,6 +84,17 @@ gn_prepare_kernel(const int64_t* __restrict__ ii, const int64_t* __restrict__ jj
   }
   __syncthreads();
   if (tid == 0) ctrl[CTRL_BAD] = s_bad | ((total != (unsigned)N) ? 2 : 0);
+  // launch order for the accumulate kernel: edges sorted by (min, max) keyframe, ties by edge id, so
+  // that (i,j) and (j,i) are adjacent and share Xs[i] / Xs[j] in L2 (rank sort, once per solve)
+  for (int e = tid; e < E; e += nt) {
+    const long long key = (long long)min(ci[e], cj[e]) * N + max(ci[e], cj[e]);
+    int rank = 0;
+    for (int f = 0; f < E; f++) {
+      const long long kf = (long long)min(ci[f], cj[f]) * N + max(ci[f], cj[f]);
+      rank += (kf < key) || (kf == key && f < e);
+    }
+    order[rank] = e;
+  }
   // incidence lists per compact pose c: entries (e << 1 | role) in ascending e; role 0: c == ci[e]
   // two passes (count, fill); self-edges contribute nothing (H_ii + H_jj - H_ij - H_ji = 0).
   for (int c = tid; c < N; c += nt) {
@@ -112,91 +123,7 @@ gn_prepare_kernel(const int64_t* __restrict__ ii, const int64_t* __restrict__ jj
 }
 
 // =============================================================================== Sim(3) retraction
-__device__ __forceinline__ void quat_mul(const float* a, const float* b, float* o) {
-  o[0] = a[3] * b[0] + a[0] * b[3] + a[1] * b[2] - a[2] * b[1];
-  o[1] = a[3] * b[1] - a[0] * b[2] + a[1] * b[3] + a[2] * b[0];
-  o[2] = a[3] * b[2] + a[0] * b[1] - a[1] * b[0] + a[2] * b[3];
-  o[3] = a[3] * b[3] - a[0] * b[0] - a[1] * b[1] - a[2] * b[2];
-}
-
-__device__ __forceinline__ void rot_act(const float* q, const float* X, float* Y) {
-  const float u0 = 2.0f * (q[1] * X[2] - q[2] * X[1]);
-  const float u1 = 2.0f * (q[2] * X[0] - q[0] * X[2]);
-  const float u2 = 2.0f * (q[0] * X[1] - q[1] * X[0]);
-  const float y0 = X[0] + q[3] * u0 + (q[1] * u2 - q[2] * u1);
-  const float y1 = X[1] + q[3] * u1 + (q[2] * u0 - q[0] * u2);
-  const float y2 = X[2] + q[3] * u2 + (q[0] * u1 - q[1] * u0);
-  Y[0] = y0; Y[1] = y1; Y[2] = y2;
-}
-
-__device__ __forceinline__ void cross_into(const float* a, float* b) {
-  const float x0 = a[1] * b[2] - a[2] * b[1];
-  const float x1 = a[2] * b[0] - a[0] * b[2];
-  const float x2 = a[0] * b[1] - a[1] * b[0];
-  b[0] = x0; b[1] = x1; b[2] = x2;
-}
-
-// T <- Exp(xi) * T, fp32, same closed form and the same 1e-6 branches as gn_kernels.cu:299-413
-__device__ void sim3_retract(const float* xi, float* T) {
-  float tau[3] = {xi[0], xi[1], xi[2]};
-  const float phi[3] = {xi[3], xi[4], xi[5]};
-  const float sigma = xi[6];
-  const float scale = expf(sigma);
-  const float theta_sq = phi[0] * phi[0] + phi[1] * phi[1] + phi[2] * phi[2];
-  float dq[4];
-  {
-    float imag, real;
-    if (theta_sq < 1e-6f) {
-      const float p4 = theta_sq * theta_sq;
-      imag = 0.5f - (1.0f / 48.0f) * theta_sq + (1.0f / 3840.0f) * p4;
-      real = 1.0f - (1.0f / 8.0f) * theta_sq + (1.0f / 384.0f) * p4;
-    } else {
-      const float th = sqrtf(theta_sq);
-      imag = sinf(0.5f * th) / th;
-      real = cosf(0.5f * th);
-    }
-    dq[0] = imag * phi[0]; dq[1] = imag * phi[1]; dq[2] = imag * phi[2]; dq[3] = real;
-  }
-  const float theta = sqrtf(theta_sq);
-  float A, B, C;
-  if (fabsf(sigma) < 1e-6f) {
-    C = 1.0f;
-    if (fabsf(theta) < 1e-6f) {
-      A = 0.5f;
-      B = 1.0f / 6.0f;
-    } else {
-      A = (1.0f - cosf(theta)) / theta_sq;
-      B = (theta - sinf(theta)) / (theta_sq * theta);
-    }
-  } else {
-    C = (scale - 1.0f) / sigma;
-    if (fabsf(theta) < 1e-6f) {
-      const float s2 = sigma * sigma;
-      A = ((sigma - 1.0f) * scale + 1.0f) / s2;
-      B = (scale * 0.5f * s2 + scale - 1.0f - sigma * scale) / (s2 * sigma);
-    } else {
-      const float a = scale * sinf(theta);
-      const float b = scale * cosf(theta);
-      const float c = theta_sq + sigma * sigma;
-      A = (a * sigma + (1.0f - b) * theta) / (theta * c);
-      B = (C - ((b - 1.0f) * sigma + a * theta) / c) / theta_sq;
-    }
-  }
-  float dt[3] = {C * tau[0], C * tau[1], C * tau[2]};
-  cross_into(phi, tau);
-  dt[0] += A * tau[0]; dt[1] += A * tau[1]; dt[2] += A * tau[2];
-  cross_into(phi, tau);
-  dt[0] += B * tau[0]; dt[1] += B * tau[1]; dt[2] += B * tau[2];
-  float q1[4], t1[3];
-  quat_mul(dq, T + 3, q1);
-  rot_act(dq, T, t1);
-  T[0] = t1[0] * scale + dt[0];
-  T[1] = t1[1] * scale + dt[1];
-  T[2] = t1[2] * scale + dt[2];
-  T[3] = q1[0]; T[4] = q1[1]; T[5] = q1[2]; T[6] = q1[3];
-  T[7] = scale * T[7];
-}
-
+// (sim3_retract lives in gn_device.cuh: it is shared with the fused tail of the accumulate kernel)
 __global__ void pose_retr_kernel(float* __restrict__ Twc, const float* __restrict__ dx, int num_kf, int num_fix) {
   for (int k = num_fix + blockIdx.x * blockDim.x + threadIdx.x; k < num_kf; k += gridDim.x * blockDim.x) {
     float T[8], xi[7];
@@ -480,13 +407,22 @@ gn_solve_kernel(const SolveArgs a) {
   }
 }
 
+// one CTA: systems with dim <= kSmallDim when the solve cannot ride in the accumulate kernel
+// (sharded runs: the all-reduce sits between the two; or the stand-alone m3r_gn_solve_retract call)
+__global__ void __launch_bounds__(kSolveThreads)
+gn_small_solve_kernel(const SmallSolveArgs a) {
+  if (a.ctrl[CTRL_DONE]) return;
+  extern __shared__ double s_small[];
+  small_solve(a, s_small);
+}
+
 int g_coop_grid = -1;  // CTAs that can be co-resident for the cooperative variant (per process)
 
 }  // namespace
 
 int launch_gn_prepare(const int64_t* ii, const int64_t* jj, const GnLayout& L, const GnPtrs& P, cudaStream_t s) {
   gn_prepare_kernel<<<1, 1024, 0, s>>>(ii, jj, L.num_edges, L.num_kf, P.ci, P.cj, P.bitmap, P.prefix,
-                                       P.inc_off, P.inc_list, P.counters, P.ctrl);
+                                       P.inc_off, P.inc_list, P.order, P.counters, P.ctrl);
   M3R_LAUNCH_CHECK();
   return M3R_OK;
 }
@@ -499,8 +435,12 @@ int launch_gn_solve(float* Twc, const GnLayout& L, const GnPtrs& P, float delta_
   a.N = L.num_kf; a.dim = L.dim; a.nblk = L.nblk; a.ld = L.ld; a.delta_thresh = delta_thresh;
   const size_t dyn = sizeof(double) * (size_t)L.nblk * kTile;
   if (dyn > 160 * 1024) return M3R_ERR_UNSUPPORTED;  // > 20k unknowns: out of scope for a dense solve
-  if (L.nblk < 3) {
-    gn_solve_kernel<false><<<1, kSolveThreads, dyn, s>>>(a);
+  if (L.dim <= kSmallDim) {
+    SmallSolveArgs ss{};
+    ss.Twc = Twc; ss.eb = P.eb; ss.ci = P.ci; ss.cj = P.cj; ss.inc_off = P.inc_off; ss.inc_list = P.inc_list;
+    ss.ctrl = P.ctrl; ss.dx_out = dx_out; ss.info_out = info_out; ss.N = L.num_kf; ss.dim = L.dim;
+    ss.delta_thresh = delta_thresh;
+    gn_small_solve_kernel<<<1, kSolveThreads, small_solve_smem_bytes(L.dim), s>>>(ss);
     M3R_LAUNCH_CHECK();
     return M3R_OK;
   }

@@ -23,14 +23,18 @@ def test_library_exports_every_declared_symbol(abi):
     for s in syms:
         assert hasattr(abi.lib, s), s
     assert set(syms) == set(abi.EXPORTS)
-    assert abi.lib.m3r_abi_version() == 1
+    assert abi.lib.m3r_abi_version() == 2
 
 
 def test_workspace_size_is_monotone(abi):
     a = abi.lib.m3r_gn_workspace_bytes(2, 2, 196608)
     b = abi.lib.m3r_gn_workspace_bytes(32, 240, 196608)
     c = abi.lib.m3r_gn_workspace_bytes(256, 2000, 196608)
-    assert 0 < a < b < c < 200 * 2 ** 20
+    # c4 on ONE rank: 2000 edges x 196608 pts x 8 B packed records = 3.1 GB of the 180 GB
+    assert 0 < a < b < c < 4 * 2 ** 30
+    # a rank that owns 1/8 of the edges keeps 1/8 of the packed slabs
+    d = abi.lib.m3r_gn_workspace_bytes_sharded(256, 2000, 196608, 250)
+    assert 0 < d < c / 4
     assert abi.lib.m3r_gn_workspace_bytes(1, 2, 10) == 0
 
 
