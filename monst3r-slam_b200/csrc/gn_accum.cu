@@ -297,9 +297,13 @@ gn_pack_kernel(const PackArgs a) {
 }
 
 template <int KIND, bool STAGED>
-__global__ void __launch_bounds__(kAccumThreads, 2)
+__global__ void __launch_bounds__(kAccumThreads, kAccumCtasPerSM)
 gn_accum_kernel(const AccumArgs a) {
-  if (a.ctrl[CTRL_DONE]) return;
+  // Programmatic dependent launch: iteration k+1 of the fused GN loop is allowed on the SMs while
+  // iteration k is still in its serial tail.  Everything up to griddepcontrol.wait touches only data
+  // that is constant during a solve (launch order, compact indices, packed records, Xs): the TMA
+  // staging of this CTA's chunk overlaps the previous iteration's reduction / solve / retraction.
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   extern __shared__ __align__(128) unsigned char dsm[];
   __shared__ __align__(8) unsigned long long s_bar[kStages];
   const int tid = threadIdx.x;
@@ -339,6 +343,13 @@ gn_accum_kernel(const AccumArgs a) {
         bulk_g2s(dst + (uint32_t)tile * 8u, Xj + (size_t)t_lo * 3, cnt * 12u, bar, pol_keep);
       }
     }
+  }
+  // from here on: poses and the stop flag written by the previous iteration
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (a.ctrl[CTRL_DONE]) {
+    if (STAGED)  // never exit with bulk copies still landing in this CTA's shared memory
+      for (int s = 0; s < ntiles; s++) mbar_wait(smem_u32(&s_bar[s]), 0);
+    return;
   }
 
   EdgeXform X;
@@ -437,7 +448,15 @@ gn_accum_kernel(const AccumArgs a) {
       const int t = tid % kAcc, sl = tid / kAcc;
       const double* p0 = a.partials + (size_t)el * a.chunks * kAcc + t;
       double s = 0.0;
-      for (int c = sl; c < a.chunks; c += 7) s += __ldcg(p0 + (size_t)c * kAcc);
+      int c = sl;
+      for (; c + 7 * 7 < a.chunks; c += 7 * 8) {  // 8 loads in flight, summed in a fixed order
+        double v[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++) v[u] = __ldcg(p0 + (size_t)(c + 7 * u) * kAcc);
+#pragma unroll
+        for (int u = 0; u < 8; u++) s += v[u];
+      }
+      for (; c < a.chunks; c += 7) s += __ldcg(p0 + (size_t)c * kAcc);
       s_part[sl][t] = s;
     }
     __syncthreads();
@@ -520,22 +539,34 @@ gn_accum_kernel(const AccumArgs a) {
   small_solve(a.ss, reinterpret_cast<double*>(dsm));
 }
 
+template <int KIND, bool STAGED>
+int launch_one(const AccumArgs& a, size_t dyn, bool pdl, cudaStream_t s) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(a.chunks, a.e_local);
+  cfg.blockDim = dim3(kAccumThreads);
+  cfg.dynamicSmemBytes = dyn;
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl ? 1 : 0;
+  M3R_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gn_accum_kernel<KIND, STAGED>, a));
+  return M3R_OK;
+}
+
 template <int KIND>
-int launch_kind(const AccumArgs& a, bool staged, size_t dyn, cudaStream_t s) {
-  dim3 grid(a.chunks, a.e_local);
+int launch_kind(const AccumArgs& a, bool staged, size_t dyn, bool pdl, cudaStream_t s) {
   if (staged) {
     static bool attr_done = false;  // per kernel instantiation
     if (!attr_done) {
       M3R_CUDA_CHECK(cudaFuncSetAttribute(gn_accum_kernel<KIND, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          kStages * 1024 * 20));
+                                          kStages * kMaxTilePts * 20));
       attr_done = true;
     }
-    gn_accum_kernel<KIND, true><<<grid, kAccumThreads, dyn, s>>>(a);
-  } else {
-    gn_accum_kernel<KIND, false><<<grid, kAccumThreads, dyn, s>>>(a);
+    return launch_one<KIND, true>(a, dyn, pdl, s);
   }
-  M3R_LAUNCH_CHECK();
-  return M3R_OK;
+  return launch_one<KIND, false>(a, dyn, pdl, s);
 }
 
 // Hs [4,E,7,7] f32 / gs [2,E,7] f32 in the reference layout, from the fp64 edge blocks
@@ -621,9 +652,9 @@ int launch_gn_accumulate(const float* Twc, const float* Xs, const float* K, cons
     if (need > dyn) dyn = need;
   }
   switch (prm.kind) {
-    case M3R_GN_POINTS: return launch_kind<M3R_GN_POINTS>(a, staged, dyn, s);
-    case M3R_GN_RAYS: return launch_kind<M3R_GN_RAYS>(a, staged, dyn, s);
-    case M3R_GN_CALIB: return launch_kind<M3R_GN_CALIB>(a, staged, dyn, s);
+    case M3R_GN_POINTS: return launch_kind<M3R_GN_POINTS>(a, staged, dyn, fuse.pdl != 0, s);
+    case M3R_GN_RAYS: return launch_kind<M3R_GN_RAYS>(a, staged, dyn, fuse.pdl != 0, s);
+    case M3R_GN_CALIB: return launch_kind<M3R_GN_CALIB>(a, staged, dyn, fuse.pdl != 0, s);
     default: return M3R_ERR_BAD_ARG;
   }
 }

@@ -14,26 +14,39 @@ constexpr int kSolveThreads = 256;
 // ctrl words (device int32)
 enum { CTRL_DONE = 0, CTRL_ITERS = 1, CTRL_FAILS = 2, CTRL_EARLY = 3, CTRL_BAD = 4, CTRL_FAIL_NOW = 5, CTRL_WORDS = 16 };
 
-// Point-chunking of one edge (pure function of (E_local, n) so that the workspace size and every
-// launch agree).  A CTA owns `chunk_pts` consecutive points of one edge, staged through shared
-// memory as up to kStages tiles of `tile_pts` points (TMA bulk copies, all issued up-front).
-//  * big graphs: 1024-point tiles, 4096-point chunks -> few edges in flight at a time, so both
-//    directions of a keyframe pair find Xs[i] / Xs[j] in the 126 MB L2;
-//  * small graphs (tracking: 2 edges): 256-point tiles so that there are >= 2 CTAs per SM.
-constexpr int kStages = 4;
+// Point-chunking of one edge: a pure function of (E, n) with E the FULL edge count, so that the
+// workspace size, every launch and every shard of a multi-GPU run agree (a shard's edge blocks are
+// then bit-identical to the unsharded run's).  A CTA owns `chunk_pts` consecutive points of one
+// edge, staged through shared memory as kStages tiles of `tile_pts` points (TMA bulk copies, all
+// issued up-front).
+//  * big graphs: 1024-point tiles -> few edges in flight at a time, so both directions of a keyframe
+//    pair find Xs[i] / Xs[j] in the 126 MB L2;
+//  * small graphs (tracking: 2 edges): the chunk shrinks until the grid is one full wave
+//    (kAccumCtasPerSM CTAs on each of the 148 SMs).
+constexpr int kStages = 3;
+constexpr int kAccumCtasPerSM = 3;
+constexpr int kMaxTilePts = 1024;
 constexpr int kSmallDim = 63;   // systems up to 9 free poses are solved inside the accumulate kernel
 struct GnChunking {
   int tile_pts, chunk_pts, chunks;
 };
-inline GnChunking gn_chunking(int num_edges_local, int n) {
+inline GnChunking gn_chunking(int num_edges, int n) {
   GnChunking c;
-  c.tile_pts = 1024;
-  const long long e = num_edges_local > 0 ? num_edges_local : 1;
-  while (c.tile_pts > 256 && e * ((n + c.tile_pts * kStages - 1) / (c.tile_pts * kStages)) < 2LL * kNumSMs)
-    c.tile_pts >>= 1;
-  c.chunk_pts = c.tile_pts * kStages;
+  const long long e = num_edges > 0 ? num_edges : 1;
+  const long long slots = (long long)kNumSMs * kAccumCtasPerSM;
+  c.chunk_pts = kMaxTilePts * kStages;
   c.chunks = (n + c.chunk_pts - 1) / c.chunk_pts;
+  if (e * c.chunks < slots) {
+    const long long per_edge = slots / e > 0 ? slots / e : 1;
+    long long chunk = (n + per_edge - 1) / per_edge;
+    chunk = (chunk + 4 * kStages - 1) / (4 * kStages) * (4 * kStages);  // tiles stay multiples of 4 points
+    if (chunk < 128 * kStages) chunk = 128 * kStages;
+    if (chunk > kMaxTilePts * kStages) chunk = kMaxTilePts * kStages;
+    c.chunk_pts = (int)chunk;
+    c.chunks = (n + c.chunk_pts - 1) / c.chunk_pts;
+  }
   if (c.chunks < 1) c.chunks = 1;
+  c.tile_pts = c.chunk_pts / kStages;
   return c;
 }
 
@@ -70,8 +83,7 @@ inline GnLayout gn_layout(int num_kf, int num_edges, int num_pts, int edges_loca
   L.off_inc_off = take(sizeof(int) * ((size_t)num_kf + 1));
   L.off_inc_list = take(sizeof(int) * 2 * (size_t)num_edges);
   L.off_order = take(sizeof(int) * (size_t)num_edges);
-  // e_local * chunks(e_local) is largest with the smallest tile: n / 1024 + 1 chunks per edge
-  const size_t worst = (size_t)num_edges * ((size_t)num_pts / (256 * kStages) + 1);
+  const size_t worst = (size_t)num_edges * (size_t)gn_chunking(num_edges, num_pts).chunks;
   L.off_partials = take(sizeof(double) * kAcc * worst);
   L.off_eb = take(sizeof(double) * kEdgeBlock * (size_t)num_edges);
   L.off_hd = take(sizeof(double) * (size_t)L.rows * L.ld);
@@ -127,6 +139,7 @@ struct GnFuse {
   int32_t* info_out;
   float delta_thresh;
   int enabled;
+  int pdl;  // launch with programmatic stream serialization (the previous op on the stream is the same kernel)
 };
 
 // entry points implemented in gn_accum.cu / gn_solve.cu (host launchers)

@@ -234,6 +234,7 @@ extern "C" int m3r_gauss_newton(float* Twc, const float* Xs, const float* Cs, co
     if (rc != M3R_OK) return rc;
   }
   for (int it = 0; it < params->max_iter; it++) {
+    fuse.pdl = fuse.enabled && it > 0;  // iteration 0 follows pack: full serialisation
     rc = accumulate_step(Twc, Xs, K, L, P, *params, shard, lo, hi, fuse, s);
     if (rc != M3R_OK) return rc;
     if (!fuse.enabled) {

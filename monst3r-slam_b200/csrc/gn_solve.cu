@@ -35,28 +35,58 @@ gn_prepare_kernel(const int64_t* __restrict__ ii, const int64_t* __restrict__ jj
                   int* __restrict__ ci, int* __restrict__ cj, unsigned* __restrict__ bitmap,
                   unsigned* __restrict__ prefix, int* __restrict__ inc_off, int* __restrict__ inc_list,
                   int* __restrict__ order, unsigned* __restrict__ counters, int* __restrict__ ctrl) {
-  constexpr int W = M3R_MAX_KF_ID / 32;
+  // presence bitmap over [id_min, id_max] only: keyframe ids are a few hundred apart at most, so the
+  // scan touches a handful of words instead of the whole M3R_MAX_KF_ID range
   const int tid = threadIdx.x, nt = blockDim.x;
   __shared__ unsigned s_scan[1024];
   __shared__ int s_bad;
-  if (tid == 0) s_bad = 0;
-  for (int k = tid; k < W; k += nt) bitmap[k] = 0u;
+  __shared__ long long s_min, s_max;
+  if (tid == 0) {
+    s_bad = 0;
+    s_min = M3R_MAX_KF_ID;
+    s_max = -1;
+  }
   for (int k = tid; k <= E; k += nt) counters[k] = 0u;
   if (tid < CTRL_WORDS) ctrl[tid] = 0;
   __syncthreads();
-  for (int k = tid; k < 2 * E; k += nt) {
-    const int64_t id = k < E ? ii[k] : jj[k - E];
-    if (id < 0 || id >= M3R_MAX_KF_ID) {
-      s_bad = 1;
-    } else {
-      atomicOr(bitmap + (id >> 5), 1u << (id & 31));
+  {
+    long long lo = M3R_MAX_KF_ID, hi = -1;
+    for (int k = tid; k < 2 * E; k += nt) {
+      const int64_t id = k < E ? ii[k] : jj[k - E];
+      if (id < 0 || id >= M3R_MAX_KF_ID) {
+        s_bad = 1;
+      } else {
+        lo = id < lo ? id : lo;
+        hi = id > hi ? id : hi;
+      }
+    }
+    for (int off = 16; off > 0; off >>= 1) {
+      const long long l2 = __shfl_xor_sync(0xffffffffu, lo, off), h2 = __shfl_xor_sync(0xffffffffu, hi, off);
+      lo = l2 < lo ? l2 : lo;
+      hi = h2 > hi ? h2 : hi;
+    }
+    if ((tid & 31) == 0) {
+      atomicMin(&s_min, lo);
+      atomicMax(&s_max, hi);
     }
   }
   __syncthreads();
-  // exclusive prefix of popcounts over W words: each thread owns W/nt consecutive words
-  const int per = W / nt;  // 32768 / 1024 = 32
+  const long long base = s_max >= 0 ? (s_min & ~31LL) : 0;  // first id of bitmap word 0
+  const int W = s_max >= 0 ? (int)((s_max - base) / 32 + 1) : 1;
+  for (int k = tid; k < W; k += nt) bitmap[k] = 0u;
+  __syncthreads();
+  for (int k = tid; k < 2 * E; k += nt) {
+    const int64_t id = k < E ? ii[k] : jj[k - E];
+    if (id >= 0 && id < M3R_MAX_KF_ID) atomicOr(bitmap + ((id - base) >> 5), 1u << ((id - base) & 31));
+  }
+  __syncthreads();
+  // exclusive prefix of popcounts over W words: each thread owns `per` consecutive words
+  const int per = (W + nt - 1) / nt;
   unsigned local = 0;
-  for (int k = 0; k < per; k++) local += __popc(bitmap[tid * per + k]);
+  for (int k = 0; k < per; k++) {
+    const int wd = tid * per + k;
+    if (wd < W) local += __popc(bitmap[wd]);
+  }
   s_scan[tid] = local;
   __syncthreads();
   for (int off = 1; off < nt; off <<= 1) {
@@ -67,16 +97,25 @@ gn_prepare_kernel(const int64_t* __restrict__ ii, const int64_t* __restrict__ jj
   }
   unsigned run = s_scan[tid] - local;
   for (int k = 0; k < per; k++) {
-    prefix[tid * per + k] = run;
-    run += __popc(bitmap[tid * per + k]);
+    const int wd = tid * per + k;
+    if (wd < W) {
+      prefix[wd] = run;
+      run += __popc(bitmap[wd]);
+    }
   }
   __syncthreads();
   const unsigned total = s_scan[nt - 1];
   for (int k = tid; k < E; k += nt) {
     const int64_t a = ii[k], b = jj[k];
     int ca = 0, cb = 0;
-    if (a >= 0 && a < M3R_MAX_KF_ID) ca = prefix[a >> 5] + __popc(bitmap[a >> 5] & ((1u << (a & 31)) - 1u));
-    if (b >= 0 && b < M3R_MAX_KF_ID) cb = prefix[b >> 5] + __popc(bitmap[b >> 5] & ((1u << (b & 31)) - 1u));
+    if (a >= 0 && a < M3R_MAX_KF_ID) {
+      const long long r = a - base;
+      ca = prefix[r >> 5] + __popc(bitmap[r >> 5] & ((1u << (r & 31)) - 1u));
+    }
+    if (b >= 0 && b < M3R_MAX_KF_ID) {
+      const long long r = b - base;
+      cb = prefix[r >> 5] + __popc(bitmap[r >> 5] & ((1u << (r & 31)) - 1u));
+    }
     if (ca >= N) { ca = 0; s_bad = 1; }
     if (cb >= N) { cb = 0; s_bad = 1; }
     ci[k] = ca;
@@ -163,45 +202,55 @@ __device__ __forceinline__ void grid_barrier() {
   }
 }
 
-// factor the 32x32 tile held in Ls (lower, stride 33) in place; returns false on a pivot <= 0
-__device__ bool tile_potrf(double (*Ls)[kTile + 1], int* s_flag) {
-  const int tid = threadIdx.x;
-  if (tid == 0) *s_flag = 0;
-  for (int j = 0; j < kTile; j++) {
-    __syncthreads();
-    if (tid == 0) {
-      const double d = Ls[j][j];
+// Factor the 32x32 tile held in Ls (lower, stride 33) and invert the factor, all by WARP 0 with the
+// tile in registers (lane r owns row r of A / L, then lane c owns column c of L^-1): no block
+// barriers inside, pivots broadcast by shuffle.  Ls <- L (upper part zeroed), Li <- L^-1.
+// Returns (to every thread, through s_flag) false on a pivot <= 0.
+__device__ bool tile_potrf_invert(double (*Ls)[kTile + 1], double (*Li)[kTile + 1], double* s_dinv, int* s_flag) {
+  const int lane = threadIdx.x;
+  if (threadIdx.x < 32) {
+    double a[kTile];
+#pragma unroll
+    for (int c = 0; c < kTile; c++) a[c] = Ls[lane][c];
+    bool bad = false;
+    double my_rinv = 1.0;
+#pragma unroll
+    for (int j = 0; j < kTile; j++) {
+      double d = __shfl_sync(0xffffffffu, a[j], j);
       if (!(d > 0.0)) {
-        *s_flag = 1;
-        Ls[j][j] = 1.0;
-      } else {
-        Ls[j][j] = sqrt(d);
+        bad = true;
+        d = 1.0;
       }
+      const double rinv = rsqrt(d);
+      const double l = a[j] * rinv;  // lane j: sqrt(d); lanes r > j: L[r][j]
+      a[j] = l;
+      if (lane == j) my_rinv = rinv;
+#pragma unroll
+      for (int c = j + 1; c < kTile; c++) a[c] -= l * __shfl_sync(0xffffffffu, l, c);
     }
-    __syncthreads();
-    if (tid > j && tid < kTile) Ls[tid][j] /= Ls[j][j];
-    __syncthreads();
-    // trailing update of the tile: entries (r, c) with j < c <= r
-    for (int t = tid; t < kTile * kTile; t += kSolveThreads) {
-      const int r = t >> 5, c = t & 31;
-      if (c > j && c <= r) Ls[r][c] -= Ls[r][j] * Ls[c][j];
+#pragma unroll
+    for (int c = 0; c < kTile; c++) Ls[lane][c] = (c <= lane) ? a[c] : 0.0;
+    s_dinv[lane] = my_rinv;
+    if (lane == 0) *s_flag = bad ? 1 : 0;
+    __syncwarp();
+    // column `lane` of L^-1 by forward substitution; L[r][m] is a shared-memory broadcast
+    double x[kTile];
+#pragma unroll
+    for (int r = 0; r < kTile; r++) {
+      double s0 = (r == lane) ? 1.0 : 0.0, s1 = 0.0;
+#pragma unroll
+      for (int m = 0; m + 1 < r; m += 2) {
+        s0 -= Ls[r][m] * x[m];
+        s1 -= Ls[r][m + 1] * x[m + 1];
+      }
+      if (r & 1) s0 -= Ls[r][r - 1] * x[r - 1];
+      x[r] = (r < lane) ? 0.0 : (s0 + s1) * s_dinv[r];
     }
+#pragma unroll
+    for (int r = 0; r < kTile; r++) Li[r][lane] = x[r];
   }
   __syncthreads();
   return *s_flag == 0;
-}
-
-// Li = L^-1 (lower triangular), one column per thread of warp 0
-__device__ void tile_invert(double (*Ls)[kTile + 1], double (*Li)[kTile + 1]) {
-  const int c = threadIdx.x;
-  if (c < kTile) {
-    for (int r = 0; r < kTile; r++) {
-      double s = (r == c) ? 1.0 : 0.0;
-      for (int m = c; m < r; m++) s -= Ls[r][m] * Li[m][c];
-      Li[r][c] = (r < c) ? 0.0 : s / Ls[r][r];
-    }
-  }
-  __syncthreads();
 }
 
 template <bool COOP>
@@ -211,6 +260,7 @@ gn_solve_kernel(const SolveArgs a) {
   __shared__ double sA[kTile][kTile + 1];
   __shared__ double sB[kTile][kTile + 1];
   __shared__ int s_flag;
+  __shared__ double s_dinv[kTile];
   __shared__ double s_red[kSolveThreads / 32];
   extern __shared__ double s_x[];  // dimP doubles (CTA 0, phase C)
 
@@ -277,8 +327,8 @@ gn_solve_kernel(const SolveArgs a) {
       const int r = t >> 5, c = t & 31;
       sA[r][c] = (c <= r) ? __ldcg(&H[(size_t)(kb * kTile + r) * ld + kb * kTile + c]) : 0.0;
     }
-    if (!tile_potrf(sA, &s_flag)) failed = true;
-    tile_invert(sA, sB);  // sB = L_kk^-1
+    __syncthreads();
+    if (!tile_potrf_invert(sA, sB, s_dinv, &s_flag)) failed = true;  // sA = L_kk, sB = L_kk^-1
     if (blockIdx.x == 0) {
       for (int t = tid; t < kTile * kTile; t += kSolveThreads) {
         const int r = t >> 5, c = t & 31;
