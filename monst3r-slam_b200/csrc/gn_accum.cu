@@ -163,7 +163,9 @@ struct AccumArgs {
   const float* Twc;
   const float* Xs;
   const float* K;
-  const uint2* packed;  // local slabs [E_local, n]: {int32 m | -1, float sqrt(Q)}
+  const uint2* packed;  // local slabs [E_local, n]: per chunk, `counts` compacted {int32 m, float sqrt(Q)}
+  const uint16_t* kloc; // chunk-local point index of each record
+  const int* counts;    // [E_local, chunks]
   const int* ci;
   const int* cj;
   const int* ctrl;
@@ -171,7 +173,7 @@ struct AccumArgs {
   unsigned* counters;   // [E] per-edge tickets, [E] (last word) = edges done in this launch
   double* partials;
   double* eb;
-  int n, e_lo, e_local, chunks, chunk_pts, tile_pts;
+  int n, e_lo, e_local, chunks, chunk_pts;
   AccumParams prm;
   int ss_counter;       // index in counters of the "edges done" ticket
   int fuse;             // 1: the last CTA of the launch solves + retracts (small systems)
@@ -244,7 +246,12 @@ __device__ __forceinline__ void edge_xform(const float* __restrict__ Ti, const f
   X.t[2] = (float)((Ri[6] * dx + Ri[7] * dy + Ri[8] * dz) * si_inv);
 }
 
-// ---- pose-independent fold: {idx, valid, Q, C_i[m], C_j[k]} -> 8-byte record, once per solve ----
+// ---- pose-independent fold + compaction, once per solve -----------------------------------------
+// Per (edge, chunk): the points that pass  valid_match && Q > Q_thresh && C_i[m] > C_thresh &&
+// C_j[k] > C_thresh  (gn_kernels.cu:953-957; none of it depends on the poses) are compacted, in
+// order, into {int32 m, float sqrt(Q)} records + their chunk-local index k (u16) + a count.  The
+// iterations then stream ~10 B per SURVIVING point instead of 13 B + two confidence gathers per point
+// and spend no instruction on rejected points.
 struct PackArgs {
   const float* Cs;
   const int64_t* idx;   // local slabs [E_local, n]
@@ -253,47 +260,92 @@ struct PackArgs {
   const int* ci;
   const int* cj;
   uint2* packed;
-  int n, e_lo;
+  uint16_t* kloc;
+  int* counts;
+  int n, e_lo, chunk_pts, chunks;
   float C_thresh, Q_thresh;
 };
 
-__device__ __forceinline__ uint2 pack_one(long long m, bool vm, float q, float cj, const float* __restrict__ Ci,
-                                          float C_thresh, float Q_thresh) {
+__device__ __forceinline__ bool pack_one(long long m, bool vm, float q, float cj, const float* __restrict__ Ci,
+                                         float C_thresh, float Q_thresh, uint2& rec) {
   // invalid matches read C_i[0] in the reference (gn_kernels.cu:913-914); the result is discarded
   const float ci = __ldg(Ci + (vm ? m : 0));
-  const bool ok = vm & (q > Q_thresh) & (ci > C_thresh) & (cj > C_thresh);
-  return make_uint2(ok ? (unsigned)(int)m : 0xffffffffu, __float_as_uint(sqrtf(q)));
+  rec = make_uint2((unsigned)(int)m, __float_as_uint(sqrtf(q)));
+  return vm & (q > Q_thresh) & (ci > C_thresh) & (cj > C_thresh);
 }
 
-template <int VEC>
+template <bool VEC4>
 __global__ void __launch_bounds__(256)
 gn_pack_kernel(const PackArgs a) {
-  const int el = blockIdx.y;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int el = blockIdx.y, chunk = blockIdx.x;
   const int e = a.e_lo + el;
   const int n = a.n;
-  const float* __restrict__ Ci = a.Cs + (size_t)a.ci[e] * n;
-  const float* __restrict__ Cj = a.Cs + (size_t)a.cj[e] * n;
+  const int ic = a.ci[e], jc = a.cj[e];
+  const float* __restrict__ Ci = a.Cs + (size_t)ic * n;
+  const float* __restrict__ Cj = a.Cs + (size_t)jc * n;
   const int64_t* __restrict__ idx = a.idx + (size_t)el * n;
   const uint8_t* __restrict__ valid = a.valid + (size_t)el * n;
   const float* __restrict__ Q = a.Q + (size_t)el * n;
-  uint2* __restrict__ out = a.packed + (size_t)el * n;
-  const size_t k0 = ((size_t)blockIdx.x * 256 + threadIdx.x) * VEC;
-  if (k0 >= (size_t)n) return;
-  if (VEC == 4) {
-    const uchar4 vm = __ldcs(reinterpret_cast<const uchar4*>(valid + k0));
-    const longlong2 m01 = __ldcs(reinterpret_cast<const longlong2*>(idx + k0));
-    const longlong2 m23 = __ldcs(reinterpret_cast<const longlong2*>(idx + k0) + 1);
-    const float4 q4 = __ldcs(reinterpret_cast<const float4*>(Q + k0));
-    const float4 c4 = __ldg(reinterpret_cast<const float4*>(Cj + k0));
-    const uint2 r0 = pack_one(m01.x, vm.x != 0, q4.x, c4.x, Ci, a.C_thresh, a.Q_thresh);
-    const uint2 r1 = pack_one(m01.y, vm.y != 0, q4.y, c4.y, Ci, a.C_thresh, a.Q_thresh);
-    const uint2 r2 = pack_one(m23.x, vm.z != 0, q4.z, c4.z, Ci, a.C_thresh, a.Q_thresh);
-    const uint2 r3 = pack_one(m23.y, vm.w != 0, q4.w, c4.w, Ci, a.C_thresh, a.Q_thresh);
-    reinterpret_cast<uint4*>(out + k0)[0] = make_uint4(r0.x, r0.y, r1.x, r1.y);
-    reinterpret_cast<uint4*>(out + k0)[1] = make_uint4(r2.x, r2.y, r3.x, r3.y);
-  } else {
-    out[k0] = pack_one(idx[k0], valid[k0] != 0, Q[k0], __ldg(Cj + k0), Ci, a.C_thresh, a.Q_thresh);
+  const int p_lo = chunk * a.chunk_pts;
+  const int p_hi = min(n, p_lo + a.chunk_pts);
+  uint2* __restrict__ out_rec = a.packed + (size_t)el * n + p_lo;
+  uint16_t* __restrict__ out_k = a.kloc + (size_t)el * n + p_lo;
+  __shared__ int s_wsum[8];
+  int base = 0;
+  if (ic != jc) {  // a self-edge contributes nothing: count 0
+    for (int pass_lo = p_lo; pass_lo < p_hi; pass_lo += 1024) {
+      const int k0 = pass_lo + tid * 4;
+      uint2 rec[4];
+      bool ok[4] = {false, false, false, false};
+      if (VEC4 && k0 + 3 < p_hi) {
+        const uchar4 vm = __ldcs(reinterpret_cast<const uchar4*>(valid + k0));
+        const longlong2 m01 = __ldcs(reinterpret_cast<const longlong2*>(idx + k0));
+        const longlong2 m23 = __ldcs(reinterpret_cast<const longlong2*>(idx + k0) + 1);
+        const float4 q4 = __ldcs(reinterpret_cast<const float4*>(Q + k0));
+        const float4 c4 = __ldg(reinterpret_cast<const float4*>(Cj + k0));
+        ok[0] = pack_one(m01.x, vm.x != 0, q4.x, c4.x, Ci, a.C_thresh, a.Q_thresh, rec[0]);
+        ok[1] = pack_one(m01.y, vm.y != 0, q4.y, c4.y, Ci, a.C_thresh, a.Q_thresh, rec[1]);
+        ok[2] = pack_one(m23.x, vm.z != 0, q4.z, c4.z, Ci, a.C_thresh, a.Q_thresh, rec[2]);
+        ok[3] = pack_one(m23.y, vm.w != 0, q4.w, c4.w, Ci, a.C_thresh, a.Q_thresh, rec[3]);
+      } else {
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+          const int k = k0 + r;
+          if (k < p_hi)
+            ok[r] = pack_one(idx[k], valid[k] != 0, Q[k], __ldg(Cj + k), Ci, a.C_thresh, a.Q_thresh, rec[r]);
+        }
+      }
+      const int cnt = (int)ok[0] + (int)ok[1] + (int)ok[2] + (int)ok[3];
+      int incl = cnt;
+#pragma unroll
+      for (int off = 1; off < 32; off <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, off);
+        if (lane >= off) incl += v;
+      }
+      if (lane == 31) s_wsum[warp] = incl;
+      __syncthreads();
+      int woff = 0, total = 0;
+#pragma unroll
+      for (int wv = 0; wv < 8; wv++) {
+        const int t = s_wsum[wv];
+        if (wv < warp) woff += t;
+        total += t;
+      }
+      int off = base + woff + incl - cnt;
+#pragma unroll
+      for (int r = 0; r < 4; r++) {
+        if (ok[r]) {
+          out_rec[off] = rec[r];
+          out_k[off] = (uint16_t)(k0 + r - p_lo);
+          off++;
+        }
+      }
+      base += total;
+      __syncthreads();
+    }
   }
+  if (tid == 0) a.counts[(size_t)el * a.chunks + chunk] = base;
 }
 
 template <int KIND, bool STAGED>
@@ -305,55 +357,56 @@ gn_accum_kernel(const AccumArgs a) {
   // staging of this CTA's chunk overlaps the previous iteration's reduction / solve / retraction.
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   extern __shared__ __align__(128) unsigned char dsm[];
-  __shared__ __align__(8) unsigned long long s_bar[kStages];
+  __shared__ __align__(8) unsigned long long s_bar;
+  __shared__ EdgeXform s_X;
   const int tid = threadIdx.x;
   const int el = a.order ? a.order[blockIdx.y] : blockIdx.y;  // local edge
   const int e = a.e_lo + el;                                   // global edge
   const int chunk = blockIdx.x;
   const int i = a.ci[e], j = a.cj[e];
   const int n = a.n;
-  const int tile = a.tile_pts;
   const int p_lo = chunk * a.chunk_pts;
-  const int p_hi = min(n, p_lo + a.chunk_pts);
-  // a self-edge contributes nothing (H_ii + H_jj - H_ij - H_ji = 0)
-  const int ntiles = (i != j && p_hi > p_lo) ? (p_hi - p_lo + tile - 1) / tile : 0;
+  const int npts = min(n, p_lo + a.chunk_pts) - p_lo;
+  const int cnt = a.counts[(size_t)el * a.chunks + chunk];  // surviving points of this chunk
 
   const float* __restrict__ Xi = a.Xs + (size_t)i * n * 3;
-  const float* __restrict__ Xj = a.Xs + (size_t)j * n * 3;
-  const uint2* __restrict__ gpk = a.packed + (size_t)el * n;
-  const uint32_t stage_bytes = (uint32_t)tile * 20u;
+  const float* __restrict__ Xj = a.Xs + ((size_t)j * n + p_lo) * 3;
+  const uint2* __restrict__ grec = a.packed + (size_t)el * n + p_lo;
+  const uint16_t* __restrict__ gk = a.kloc + (size_t)el * n + p_lo;
+  // smem: Xs[j] chunk (12 B/pt) | records (8 B) | local indices (2 B); chunk_pts % 8 == 0 keeps all 16-B aligned
+  const uint32_t off_rec = (uint32_t)a.chunk_pts * 12u, off_k = (uint32_t)a.chunk_pts * 20u;
 
   if (STAGED) {
     if (tid == 0) {
-#pragma unroll
-      for (int s = 0; s < kStages; s++) mbar_init(smem_u32(&s_bar[s]), 1);
+      mbar_init(smem_u32(&s_bar), 1);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    __syncthreads();
-    if (tid == 0) {
-      const uint64_t pol_stream = l2_policy_evict_first();  // records are read once per iteration
-      const uint64_t pol_keep = l2_policy_evict_last();     // Xs[j] is re-read by the other edges of j
-      for (int s = 0; s < ntiles; s++) {
-        const int t_lo = p_lo + s * tile;
-        const uint32_t cnt = (uint32_t)min(tile, p_hi - t_lo);
-        const uint32_t bar = smem_u32(&s_bar[s]);
-        const uint32_t dst = smem_u32(dsm) + (uint32_t)s * stage_bytes;
-        mbar_expect_tx(bar, cnt * 20u);
-        bulk_g2s(dst, gpk + t_lo, cnt * 8u, bar, pol_stream);
-        bulk_g2s(dst + (uint32_t)tile * 8u, Xj + (size_t)t_lo * 3, cnt * 12u, bar, pol_keep);
+      if (cnt > 0) {
+        const uint64_t pol_stream = l2_policy_evict_first();  // records are read once per iteration
+        const uint64_t pol_keep = l2_policy_evict_last();     // Xs[j] is re-read by the other edges of j
+        const uint32_t cnt8 = ((uint32_t)cnt + 7u) & ~7u;     // <= chunk_pts; the pad is never read back
+        const uint32_t bar = smem_u32(&s_bar);
+        const uint32_t dst = smem_u32(dsm);
+        mbar_expect_tx(bar, (uint32_t)npts * 12u + cnt8 * 10u);
+        bulk_g2s(dst, Xj, (uint32_t)npts * 12u, bar, pol_keep);
+        bulk_g2s(dst + off_rec, grec, cnt8 * 8u, bar, pol_stream);
+        bulk_g2s(dst + off_k, gk, cnt8 * 2u, bar, pol_stream);
       }
     }
   }
   // from here on: poses and the stop flag written by the previous iteration
   asm volatile("griddepcontrol.wait;" ::: "memory");
-  if (a.ctrl[CTRL_DONE]) {
-    if (STAGED)  // never exit with bulk copies still landing in this CTA's shared memory
-      for (int s = 0; s < ntiles; s++) mbar_wait(smem_u32(&s_bar[s]), 0);
+  const int done = a.ctrl[CTRL_DONE];
+  if (tid == 0 && !done) edge_xform(a.Twc + (size_t)i * 8, a.Twc + (size_t)j * 8, s_X);
+  __syncthreads();  // s_X, and the mbarrier init
+  if (done) {
+    if (STAGED && cnt > 0) mbar_wait(smem_u32(&s_bar), 0);  // never exit with bulk copies still landing here
     return;
   }
-
   EdgeXform X;
-  edge_xform(a.Twc + (size_t)i * 8, a.Twc + (size_t)j * 8, X);
+#pragma unroll
+  for (int t = 0; t < 9; t++) X.m[t] = s_X.m[t];
+#pragma unroll
+  for (int t = 0; t < 3; t++) X.t[t] = s_X.t[t];
   AccumParams prm = a.prm;
   if (KIND == M3R_GN_CALIB) {  // K[0][0], K[1][1], K[0][2], K[1][2] (gn_kernels.cu:1274-1279)
     prm.fx = __ldg(a.K + 0);
@@ -366,47 +419,54 @@ gn_accum_kernel(const AccumArgs a) {
 #pragma unroll
   for (int t = 0; t < kAcc; t++) acc[t] = 0.f;
 
-  for (int s = 0; s < ntiles; s++) {
-    const int t_lo = p_lo + s * tile;
-    const int cnt = min(tile, p_hi - t_lo);
-    const uint2* spk;
+  if (cnt > 0) {
     const float* sx;
+    const uint2* srec;
+    const uint16_t* sk;
     if (STAGED) {
-      mbar_wait(smem_u32(&s_bar[s]), 0);
-      spk = reinterpret_cast<const uint2*>(dsm + (size_t)s * stage_bytes);
-      sx = reinterpret_cast<const float*>(dsm + (size_t)s * stage_bytes + (size_t)tile * 8);
+      mbar_wait(smem_u32(&s_bar), 0);
+      sx = reinterpret_cast<const float*>(dsm);
+      srec = reinterpret_cast<const uint2*>(dsm + off_rec);
+      sk = reinterpret_cast<const uint16_t*>(dsm + off_k);
     } else {
-      spk = gpk + t_lo;
-      sx = Xj + (size_t)t_lo * 3;
+      sx = Xj;
+      srec = grec;
+      sk = gk;
     }
     for (int k0 = tid; k0 < cnt; k0 += 4 * kAccumThreads) {
-      int m[4];
+      int m[4], kl[4];
       float sq[4], xi[4][3];
 #pragma unroll
       for (int r = 0; r < 4; r++) {
         const int k = k0 + r * kAccumThreads;
-        uint2 rec = make_uint2(0xffffffffu, 0u);
-        if (k < cnt) rec = spk[k];
-        m[r] = (int)rec.x;
-        sq[r] = __uint_as_float(rec.y);
+        m[r] = -1;
+        if (k < cnt) {
+          const uint2 rec = srec[k];
+          m[r] = (int)rec.x;
+          sq[r] = __uint_as_float(rec.y);
+          kl[r] = sk[k];
+        }
       }
-      // all gathers of this pass are in flight before any arithmetic (record 0 for masked points)
+      // all gathers of this pass are in flight before any arithmetic
 #pragma unroll
       for (int r = 0; r < 4; r++) {
-        const float* g = Xi + (size_t)max(m[r], 0) * 3;
-        xi[r][0] = __ldg(g + 0);
-        xi[r][1] = __ldg(g + 1);
-        xi[r][2] = __ldg(g + 2);
+        if (m[r] >= 0) {
+          const float* g = Xi + (size_t)m[r] * 3;
+          xi[r][0] = __ldg(g + 0);
+          xi[r][1] = __ldg(g + 1);
+          xi[r][2] = __ldg(g + 2);
+        }
       }
 #pragma unroll
       for (int r = 0; r < 4; r++) {
         if (m[r] >= 0) {
-          const float* xj = sx + (size_t)(k0 + r * kAccumThreads) * 3;
+          const float* xj = sx + kl[r] * 3;
           accum_point<KIND>(acc, X, prm, xj[0], xj[1], xj[2], sq[r], m[r], xi[r][0], xi[r][1], xi[r][2]);
         }
       }
     }
   }
+
   // ---- CTA reduction: shuffles -> smem -> fp64 partial ----
   __shared__ float s_warp[kAccumThreads / 32][kAcc];
   __shared__ double s_part[7][kAcc];
@@ -415,8 +475,22 @@ gn_accum_kernel(const AccumArgs a) {
   __shared__ double s_T[56];
   __shared__ bool s_last;
   const int lane = tid & 31, warp = tid >> 5;
+  // terms 0..31: transposing butterfly (31 shuffles instead of 160): after the step with offset
+  // `off`, slot i of a lane holds the sum over its xor-group of term i | (lane & off); lane l ends
+  // up with the warp total of term l.  Terms 32..34: plain butterflies.
 #pragma unroll
-  for (int t = 0; t < kAcc; t++) {
+  for (int off = 16; off > 0; off >>= 1) {
+    const bool up = (lane & off) != 0;
+#pragma unroll
+    for (int t = 0; t < off; t++) {
+      const float send = up ? acc[t] : acc[t + off];
+      const float keep = up ? acc[t + off] : acc[t];
+      acc[t] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+    }
+  }
+  s_warp[warp][lane] = acc[0];
+#pragma unroll
+  for (int t = 32; t < kAcc; t++) {
     float v = acc[t];
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
@@ -561,7 +635,7 @@ int launch_kind(const AccumArgs& a, bool staged, size_t dyn, bool pdl, cudaStrea
     static bool attr_done = false;  // per kernel instantiation
     if (!attr_done) {
       M3R_CUDA_CHECK(cudaFuncSetAttribute(gn_accum_kernel<KIND, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          kStages * kMaxTilePts * 20));
+                                          kMaxChunkPts * 22));
       attr_done = true;
     }
     return launch_one<KIND, true>(a, dyn, pdl, s);
@@ -601,13 +675,13 @@ int launch_gn_pack(const float* Cs, const int64_t* idx, const uint8_t* valid, co
   const bool vec4 = (L.num_pts % 4 == 0) &&
                     ((reinterpret_cast<uintptr_t>(Cs) | reinterpret_cast<uintptr_t>(idx) |
                       reinterpret_cast<uintptr_t>(Q) | reinterpret_cast<uintptr_t>(valid)) % 16 == 0);
-  if (vec4) {
-    dim3 grid((L.num_pts / 4 + 255) / 256, e_local);
-    gn_pack_kernel<4><<<grid, 256, 0, s>>>(a);
-  } else {
-    dim3 grid((L.num_pts + 255) / 256, e_local);
-    gn_pack_kernel<1><<<grid, 256, 0, s>>>(a);
-  }
+  const GnChunking ck = gn_chunking(L.num_edges, L.num_pts);
+  a.kloc = P.kloc; a.counts = P.counts; a.chunk_pts = ck.chunk_pts; a.chunks = ck.chunks;
+  dim3 grid(ck.chunks, e_local);
+  if (vec4)
+    gn_pack_kernel<true><<<grid, 256, 0, s>>>(a);
+  else
+    gn_pack_kernel<false><<<grid, 256, 0, s>>>(a);
   M3R_LAUNCH_CHECK();
   return M3R_OK;
 }
@@ -625,7 +699,7 @@ int launch_gn_accumulate(const float* Twc, const float* Xs, const float* K, cons
   a.e_local = e_local;
   // chunking depends on the FULL edge count, so a shard's blocks are bit-identical to the unsharded run's
   const GnChunking ck = gn_chunking(L.num_edges, L.num_pts);
-  a.chunks = ck.chunks; a.chunk_pts = ck.chunk_pts; a.tile_pts = ck.tile_pts;
+  a.chunks = ck.chunks; a.chunk_pts = ck.chunk_pts; a.kloc = P.kloc; a.counts = P.counts;
   a.ss_counter = L.num_edges;
   a.order = (e_lo == 0 && e_hi == L.num_edges) ? P.order : nullptr;  // shards are pre-ordered by the host
   a.prm.inv_sigma_a = (float)(1.0 / (double)prm.sigma_a);
@@ -639,9 +713,9 @@ int launch_gn_accumulate(const float* Twc, const float* Xs, const float* K, cons
   a.prm.v_lo = (float)prm.pixel_border;
   a.prm.v_hi = (float)(prm.height - 1 - prm.pixel_border);
   if (prm.kind == M3R_GN_CALIB && !K) return M3R_ERR_BAD_ARG;  // read on the device: the call stays asynchronous
-  // TMA bulk copies need 16-byte aligned sources and sizes: n % 4 == 0 makes every tile of both streams so
-  const bool staged = (L.num_pts % 4 == 0) && (reinterpret_cast<uintptr_t>(Xs) % 16 == 0);
-  size_t dyn = staged ? (size_t)kStages * ck.tile_pts * 20 : 0;
+  // TMA bulk copies need 16-byte aligned sources and sizes: n % 8 == 0 makes every chunk of all three streams so
+  const bool staged = (L.num_pts % 8 == 0) && (reinterpret_cast<uintptr_t>(Xs) % 16 == 0);
+  size_t dyn = staged ? (size_t)ck.chunk_pts * 22 : 0;
   a.fuse = 0;
   if (fuse.enabled && L.dim <= kSmallDim && e_lo == 0 && e_hi == L.num_edges) {
     a.fuse = 1;

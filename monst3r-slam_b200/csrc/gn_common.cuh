@@ -16,37 +16,33 @@ enum { CTRL_DONE = 0, CTRL_ITERS = 1, CTRL_FAILS = 2, CTRL_EARLY = 3, CTRL_BAD =
 
 // Point-chunking of one edge: a pure function of (E, n) with E the FULL edge count, so that the
 // workspace size, every launch and every shard of a multi-GPU run agree (a shard's edge blocks are
-// then bit-identical to the unsharded run's).  A CTA owns `chunk_pts` consecutive points of one
-// edge, staged through shared memory as kStages tiles of `tile_pts` points (TMA bulk copies, all
-// issued up-front).
-//  * big graphs: 1024-point tiles -> few edges in flight at a time, so both directions of a keyframe
-//    pair find Xs[i] / Xs[j] in the 126 MB L2;
+// then bit-identical to the unsharded run's).  A CTA owns `chunk_pts` consecutive points of one edge.
+//  * big graphs: 3072-point chunks -> few edges in flight at a time, so both directions of a
+//    keyframe pair find Xs[i] / Xs[j] in the 126 MB L2;
 //  * small graphs (tracking: 2 edges): the chunk shrinks until the grid is one full wave
 //    (kAccumCtasPerSM CTAs on each of the 148 SMs).
-constexpr int kStages = 3;
 constexpr int kAccumCtasPerSM = 3;
-constexpr int kMaxTilePts = 1024;
-constexpr int kSmallDim = 63;   // systems up to 9 free poses are solved inside the accumulate kernel
+constexpr int kMaxChunkPts = 3072;  // x 22 B (Xs[j] 12 + record 8 + local index 2) = 66 KB of smem per CTA
+constexpr int kSmallDim = 63;       // systems up to 9 free poses are solved inside the accumulate kernel
 struct GnChunking {
-  int tile_pts, chunk_pts, chunks;
+  int chunk_pts, chunks;
 };
 inline GnChunking gn_chunking(int num_edges, int n) {
   GnChunking c;
   const long long e = num_edges > 0 ? num_edges : 1;
   const long long slots = (long long)kNumSMs * kAccumCtasPerSM;
-  c.chunk_pts = kMaxTilePts * kStages;
+  c.chunk_pts = kMaxChunkPts;
   c.chunks = (n + c.chunk_pts - 1) / c.chunk_pts;
   if (e * c.chunks < slots) {
     const long long per_edge = slots / e > 0 ? slots / e : 1;
     long long chunk = (n + per_edge - 1) / per_edge;
-    chunk = (chunk + 4 * kStages - 1) / (4 * kStages) * (4 * kStages);  // tiles stay multiples of 4 points
-    if (chunk < 128 * kStages) chunk = 128 * kStages;
-    if (chunk > kMaxTilePts * kStages) chunk = kMaxTilePts * kStages;
+    chunk = (chunk + 7) / 8 * 8;  // 16-byte granularity for every staged stream
+    if (chunk < 256) chunk = 256;
+    if (chunk > kMaxChunkPts) chunk = kMaxChunkPts;
     c.chunk_pts = (int)chunk;
     c.chunks = (n + c.chunk_pts - 1) / c.chunk_pts;
   }
   if (c.chunks < 1) c.chunks = 1;
-  c.tile_pts = c.chunk_pts / kStages;
   return c;
 }
 
@@ -54,7 +50,7 @@ struct GnLayout {
   int num_kf, num_edges, num_pts;
   int dim, nblk, ld, rows;  // system dim 7(N-1); tiles; leading dimension; rows incl. rhs tile row
   size_t off_ctrl, off_counters, off_ci, off_cj, off_bitmap, off_prefix, off_inc_off, off_inc_list,
-      off_order, off_partials, off_eb, off_hd, off_linv, off_packed, off_total;
+      off_order, off_partials, off_eb, off_hd, off_linv, off_counts, off_kloc, off_packed, off_total;
   int edges_local;  // packed slabs are sized for this many edges (== num_edges unless sharded)
 };
 
@@ -88,9 +84,12 @@ inline GnLayout gn_layout(int num_kf, int num_edges, int num_pts, int edges_loca
   L.off_eb = take(sizeof(double) * kEdgeBlock * (size_t)num_edges);
   L.off_hd = take(sizeof(double) * (size_t)L.rows * L.ld);
   L.off_linv = take(sizeof(double) * (size_t)L.nblk * kTile * kTile);
-  // packed per-point records {int32 m | -1, float sqrt(Q)} of the locally owned edges (last region)
+  // compacted per-point records of the locally owned edges (last regions): per (edge, chunk) a count,
+  // then for each surviving point its chunk-local index (u16) and {int32 m, float sqrt(Q)}
   L.edges_local = edges_local < 0 ? num_edges : edges_local;
-  L.off_packed = take(sizeof(uint2) * (size_t)L.edges_local * (size_t)num_pts);
+  L.off_counts = take(sizeof(int) * (size_t)L.edges_local * (size_t)gn_chunking(num_edges, num_pts).chunks);
+  L.off_kloc = take(sizeof(uint16_t) * ((size_t)L.edges_local * (size_t)num_pts + 8));
+  L.off_packed = take(sizeof(uint2) * ((size_t)L.edges_local * (size_t)num_pts + 8));
   L.off_total = o;
   return L;
 }
@@ -110,6 +109,8 @@ struct GnPtrs {
   double* hd;
   double* linv;
   uint2* packed;
+  uint16_t* kloc;
+  int* counts;
 };
 
 inline GnPtrs gn_ptrs(const GnLayout& L, void* ws) {
@@ -129,6 +130,8 @@ inline GnPtrs gn_ptrs(const GnLayout& L, void* ws) {
   p.hd = reinterpret_cast<double*>(b + L.off_hd);
   p.linv = reinterpret_cast<double*>(b + L.off_linv);
   p.packed = reinterpret_cast<uint2*>(b + L.off_packed);
+  p.kloc = reinterpret_cast<uint16_t*>(b + L.off_kloc);
+  p.counts = reinterpret_cast<int*>(b + L.off_counts);
   return p;
 }
 

@@ -85,7 +85,7 @@ int check_common(int num_kf, int num_pts, int num_edges, const void* ws, size_t 
   }
   *L = gn_layout(num_kf, num_edges, num_pts, e_local);
   // calls without shard information (prepare / solve / export) never touch the packed slabs
-  if (ws_bytes < (needs_packed ? L->off_total : L->off_packed)) return M3R_ERR_WORKSPACE;
+  if (ws_bytes < (needs_packed ? L->off_total : L->off_counts)) return M3R_ERR_WORKSPACE;
   return M3R_OK;
 }
 
