@@ -17,7 +17,7 @@ LIB = os.path.join(HERE, "lib")
 INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 
 CU_SOURCES = ["iter_proj.cu", "refine_matches.cu", "gn_accum.cu", "gn_solve.cu", "gn_driver.cu"]
-HEADERS = ["common.cuh", "gn_common.cuh"]
+HEADERS = ["common.cuh", "gn_common.cuh", "tma.cuh", "gn_device.cuh"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--expt-relaxed-constexpr"]
 HOST_CXX = "/usr/bin/g++"

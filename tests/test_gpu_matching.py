@@ -111,6 +111,72 @@ def test_refine_borders_zero_descriptors_generic_fdim(backends, oracle):
         assert np.array_equal(np_(out), want), (radius, dil)
 
 
+def _staged_case(h, w, kind, seed, b=1, quant=False):
+    """n == h*w queries (the staged shared-memory path) with start pixels of a given structure"""
+    g = torch.Generator().manual_seed(seed)
+    D11 = torch.randn(b, h, w, 24, generator=g)
+    D11 = torch.nn.functional.avg_pool2d(D11.permute(0, 3, 1, 2), 5, 1, 2).permute(0, 2, 3, 1).contiguous()
+    D11 = D11 / D11.norm(dim=-1, keepdim=True)
+    if quant:  # few distinct values -> many exactly tied scores: the scan order decides
+        D11 = (D11 * 2).round() / 2
+    vv, uu = torch.meshgrid(torch.arange(h), torch.arange(w), indexing="ij")
+    uu, vv = uu.float(), vv.float()
+    if kind == "shift":
+        pu, pv = uu + 7, vv - 4
+    elif kind == "zoom":  # 1.7x magnification about the centre: boxes exceed one pass
+        pu, pv = (uu - w / 2) * 1.7 + w / 2, (vv - h / 2) * 1.7 + h / 2
+    elif kind == "shrink":
+        pu, pv = (uu - w / 2) * 0.3 + w / 2, (vv - h / 2) * 0.3 + h / 2
+    elif kind == "random":
+        pu, pv = torch.rand(h, w, generator=g) * w, torch.rand(h, w, generator=g) * h
+    elif kind == "mixed":  # smooth flow + 8 % far outliers + a few out-of-image / absurd starts
+        pu = uu + 5 * torch.sin(vv / 9) + 3
+        pv = vv + 4 * torch.cos(uu / 11) - 2
+        out = torch.rand(h, w, generator=g) < 0.08
+        pu = torch.where(out, torch.rand(h, w, generator=g) * w, pu)
+        pv = torch.where(out, torch.rand(h, w, generator=g) * h, pv)
+    p1 = torch.stack((pu, pv), -1).round().long().view(1, h * w, 2).repeat(b, 1, 1)
+    if kind == "mixed" and h * w > 303:
+        p1[:, 5] = torch.tensor([-3, 2]); p1[:, 77] = torch.tensor([w + 2, h + 9]); p1[:, 300] = torch.tensor([-100000, 5])
+        p1[:, 301] = torch.tensor([3, 2 ** 20]); p1[:, 302] = torch.tensor([w - 1, h - 1]); p1[:, 303] = torch.tensor([0, 0])
+    elif kind != "mixed":
+        p1[..., 0].clamp_(0, w - 1); p1[..., 1].clamp_(0, h - 1)
+    qsrc = p1.clone(); qsrc[..., 0].clamp_(0, w - 1); qsrc[..., 1].clamp_(0, h - 1)
+    jit = torch.randint(-6, 7, qsrc.shape, generator=g)
+    qsrc = qsrc + jit; qsrc[..., 0].clamp_(0, w - 1); qsrc[..., 1].clamp_(0, h - 1)
+    bi = torch.arange(b).view(b, 1).expand(b, h * w)
+    D21 = D11[bi, qsrc[..., 1], qsrc[..., 0]] + 0.02 * torch.randn(b, h * w, 24, generator=g)
+    return D11.half().cuda(), D21.half().cuda().contiguous(), p1.cuda().contiguous()
+
+
+@pytest.mark.parametrize("kind,h,w,dil,quant", [
+    ("shift", 64, 96, 5, False), ("zoom", 64, 96, 5, False), ("shrink", 64, 96, 5, False),
+    ("random", 64, 96, 5, False), ("mixed", 64, 96, 5, False), ("mixed", 50, 70, 5, True),
+    ("shift", 33, 47, 8, True), ("zoom", 50, 70, 1, True), ("mixed", 16, 16, 3, False), ("shift", 7, 5, 5, False)])
+def test_refine_staged_path_bit_exact(backends, oracle, kind, h, w, dil, quant):
+    """every route through refine_staged_kernel (single pass, column passes, robust inlier box,
+    global-gather outliers, border checks, partial tiles) against the oracle, bit for bit"""
+    need_gpu()
+    D11, D21, p1 = _staged_case(h, w, kind, seed=31 + h + dil, b=2, quant=quant)
+    (out,) = backends.refine_matches(D11, D21, p1, 3, dil)
+    want = oracle.refine_matches(np_(D11), np_(D21), np_(p1), 3, dil)
+    bad = (np_(out) != want).any(-1)
+    assert not bad.any(), (kind, int(bad.sum()), np.argwhere(bad)[:5], np_(out)[bad][:5], want[bad][:5])
+
+
+def test_refine_staged_equals_gather_full_size(backends):
+    """512x384: the staged kernel (n == h*w) and the global-gather kernel (same queries presented as
+    two half-length lists, n != h*w) must agree exactly"""
+    need_gpu()
+    h, w = 384, 512
+    D11, D21, p1 = _staged_case(h, w, "mixed", seed=99)
+    (a,) = backends.refine_matches(D11, D21, p1, 3, 5)
+    n2 = h * w // 2
+    (b0,) = backends.refine_matches(D11, D21[:, :n2].contiguous(), p1[:, :n2].contiguous(), 3, 5)
+    (b1,) = backends.refine_matches(D11, D21[:, n2:].contiguous(), p1[:, n2:].contiguous(), 3, 5)
+    assert torch.equal(a, torch.cat((b0, b1), 1))
+
+
 def test_refine_vs_reference_cuda_full_size(backends, ref_backends, synth):
     need_gpu()
     h, w = 384, 512

@@ -60,6 +60,38 @@ __global__ void k_hmul_hadd(float* out, float a, float b) {
   out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
+// the refine_matches inner mix: 1 PRMT (alu pipe) + 1 HMUL2 + 1 HADD2 (fma pipe) per step
+__global__ void k_prmt_hmul_hadd(float* out, float a, float b) {
+  __half2 acc[ILP];
+  unsigned x[ILP];
+  for (int i = 0; i < ILP; i++) { acc[i] = __floats2half2_rn(threadIdx.x + i, 1.0f); x[i] = threadIdx.x * 0x01010101u + i; }
+  const __half2 a2 = __floats2half2_rn(a, a);
+  for (int it = 0; it < ITERS; it++) {
+#pragma unroll
+    for (int i = 0; i < ILP; i++) {
+      x[i] = __byte_perm(x[i], x[(i + 1) % ILP], 0x5410 + (it & 1));
+      acc[i] = __hadd2_rn(acc[i], __hmul2_rn(*reinterpret_cast<__half2*>(&x[i]), a2));
+    }
+  }
+  float s = 0;
+  for (int i = 0; i < ILP; i++) s += __low2float(acc[i]) + __high2float(acc[i]);
+  out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+// HADD2 only (dependent chain per acc, ILP independent chains)
+__global__ void k_hadd(float* out, float a, float b) {
+  __half2 acc[ILP];
+  for (int i = 0; i < ILP; i++) acc[i] = __floats2half2_rn(threadIdx.x + i, 1.0f);
+  const __half2 b2 = __floats2half2_rn(b, b);
+  for (int it = 0; it < ITERS; it++) {
+#pragma unroll
+    for (int i = 0; i < ILP; i++) acc[i] = __hadd2_rn(acc[i], b2);
+  }
+  float s = 0;
+  for (int i = 0; i < ILP; i++) s += __low2float(acc[i]) + __high2float(acc[i]);
+  out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
 template <typename F>
 void run(const char* name, F launch, double inst_per_thread) {
   cudaEvent_t e0, e1;
@@ -92,6 +124,8 @@ int main() {
   run("FFMA2", [&] { k_ffma2<<<g, b>>>(out, 1.0001f, 0.5f); }, (double)ITERS * ILP);
   run("FFMA2+2ALU", [&] { k_ffma2_alu<<<g, b>>>(out, 1.0001f, 0.5f); }, (double)ITERS * ILP * 3);
   run("HMUL2+HADD2", [&] { k_hmul_hadd<<<g, b>>>(out, 1.0001f, 0.5f); }, (double)ITERS * ILP * 2);
+  run("HADD2", [&] { k_hadd<<<g, b>>>(out, 1.0001f, 0.5f); }, (double)ITERS * ILP);
+  run("PRMT+HMUL2+HADD2", [&] { k_prmt_hmul_hadd<<<g, b>>>(out, 1.0001f, 0.5f); }, (double)ITERS * ILP * 3);
   printf("%s\n", cudaGetErrorString(cudaGetLastError()));
   return 0;
 }
