@@ -360,27 +360,32 @@ refine_staged_kernel(const __half* __restrict__ D11, const __half* __restrict__ 
     const int bh = py1 - py0 + 1;
     // ---- passes over groups of u-offset columns -------------------------------------------------
     if (have_box && bh > 0) {
+      // Row pitch = width rounded up to 8 px (384 B): a 16-byte chunk of pixel (x, y) then lands in bank
+      // group (3x + t) mod 8 whatever y is, so the 8 lanes of an LDS.128 wavefront stay conflict-free
+      // when neighbouring queries' centres sit on different rows.
       const int spanu = umax - umin + 1;
-      const int cmax = (kCapPx / bh - spanu) / d + 1;  // >= 1 by construction
+      const int cmax = ((kCapPx / bh) / 8 * 8 - spanu) / d + 1;
       for (int i0 = 0; i0 < kStCnt;) {
-        const int c = min(kStCnt - i0, cmax);
+        const int c = max(1, min(kStCnt - i0, cmax));
         const int px0 = max(umin - rd + i0 * d, 0);
         const int px1 = min(umax - rd + (i0 + c - 1) * d, w - 1);
         const int pw = px1 - px0 + 1;
         if (pw > 0) {  // block-uniform
+          int pitch = (pw + 7) & ~7;
+          if (pitch * bh > kCapPx) pitch = pw;  // (only when cmax < 1: a single column that just fits unpadded)
           const uint32_t rowbytes = static_cast<uint32_t>(pw) * kPxBytes;
           __syncthreads();  // every thread is done reading the previous box
           if (tid == 0) mbar_expect_tx(bar, rowbytes * static_cast<uint32_t>(bh));
           for (int r = tid; r < bh; r += kStThreads)
-            bulk_g2s(smem_u32(sbox) + r * rowbytes, img + (static_cast<size_t>(py0 + r) * w + px0) * kPxBytes,
-                     rowbytes, bar, pol);
+            bulk_g2s(smem_u32(sbox) + r * pitch * kPxBytes,
+                     img + (static_cast<size_t>(py0 + r) * w + px0) * kPxBytes, rowbytes, bar, pol);
           mbar_wait(bar, phase);
           phase ^= 1u;
           const bool interior = u0 - rd >= 0 && u0 + rd < w && v0 - rd >= 0 && v0 + rd < h;
           const bool fast = __all_sync(0xffffffffu, !inl || interior);
           if (inl) {
-            const int base = ((v0 - rd - py0) * pw + (u0 - rd - px0)) * kPxBytes;
-            const int rowstep = d * pw * kPxBytes, colstep = d * kPxBytes;
+            const int base = ((v0 - rd - py0) * pitch + (u0 - rd - px0)) * kPxBytes;
+            const int rowstep = d * pitch * kPxBytes, colstep = d * kPxBytes;
             int bc = -1;
             if (fast)
               staged_columns<false>(q, sbox, base, rowstep, colstep, i0, c, u0, v0, rd, d, w, h, best, bc);
