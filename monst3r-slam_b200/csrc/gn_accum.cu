@@ -28,7 +28,13 @@
 //    system and retracts the poses (gn_device.cuh: small_solve), i.e. ONE launch per GN iteration.
 //
 // H_ii = H_jj = A_e, H_ij = H_ji = -A_e, g_i = -b_e, g_j = +b_e (gn_kernels.cu:1096-1137).
+#include <cooperative_groups.h>
+
+#include <algorithm>
+#include <atomic>
+
 #include "gn_device.cuh"
+#include "tma.cuh"
 
 namespace m3r {
 namespace {
@@ -179,44 +185,6 @@ struct AccumArgs {
   int fuse;             // 1: the last CTA of the launch solves + retracts (small systems)
   SmallSolveArgs ss;
 };
-
-// ---- TMA bulk copy + mbarrier (PTX; SASS: UBLKCP / SYNCS) --------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t phase) {
-  uint32_t done = 0;
-  while (!done) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(done)
-        : "r"(bar), "r"(phase)
-        : "memory");
-  }
-}
-__device__ __forceinline__ uint64_t l2_policy_evict_first() {
-  uint64_t pol;
-  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
-  return pol;
-}
-__device__ __forceinline__ uint64_t l2_policy_evict_last() {
-  uint64_t pol;
-  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
-  return pol;
-}
-// global -> shared bulk copy; bytes % 16 == 0, both addresses 16-byte aligned
-__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar, uint64_t pol) {
-  asm volatile(
-      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
-      ::"r"(dst), "l"(src), "r"(bytes), "r"(bar), "l"(pol)
-      : "memory");
-}
 
 // relative pose T_ij = T_i^-1 T_j in fp64 -> fp32 3x4
 __device__ __forceinline__ void edge_xform(const float* __restrict__ Ti, const float* __restrict__ Tj, EdgeXform& X) {
@@ -613,6 +581,411 @@ gn_accum_kernel(const AccumArgs a) {
   small_solve(a.ss, reinterpret_cast<double*>(dsm));
 }
 
+
+// ---- persistent tracking kernel ------------------------------------------------------------------
+// Tracking-sized problems (<= kTrackMaxEdges directed edges, all of a CTA's points fit in shared
+// memory): the whole Gauss-Newton loop is ONE cooperative launch with one CTA per SM.  A CTA stages
+// its share of one edge ONCE (TMA bulk copies of the packed records and Xs[j], then a gather of the
+// pose-independent Xs[i][m] into shared memory), so the iterations never touch HBM or L2 for point
+// data.  Per iteration: accumulate from shared memory -> one fp64 partial per CTA -> grid barrier ->
+// EVERY CTA sums the partials in the same fixed order, applies the adjoints, solves the small system
+// and retracts its own shared-memory copy of the poses (bit-identical in all CTAs, so there is no
+// second barrier and no broadcast); CTA 0 writes dx / Twc / info.  Replaces max_iter launches of
+// gn_accum_kernel (each ~20 us of launch + staging + last-CTA serial tail at 2 x 196 608 points).
+#ifdef M3R_TRACK_PROF
+__device__ unsigned long long g_dbg[1024];
+#define TRK(slot)                                                     \
+  do {                                                                \
+    if (blockIdx.x == 0 && tid == 0) {                                \
+      const long long now_ = clock64();                               \
+      a.ss.ctrl[6 + (slot)] += (int)(now_ - trk_t);                      \
+      trk_t = now_;                                                   \
+    }                                                                 \
+  } while (0)
+#else
+#define TRK(slot) do { } while (0)
+#endif
+constexpr int kTrackThreads = 512;
+constexpr int kTrackMaxEdges = 8;
+constexpr int kTrackPtBytes = 34;  // Xs[j] 12 | record 8 | local index 2 | gathered Xs[i][m] 12
+constexpr int kTrackMaxPts = 4800; // x 34 B = 163 KB staged + 33 KB solve + 33 KB static <= 227 KB per CTA
+
+struct TrackArgs {
+  AccumArgs a;
+  int cpe, upc;       // CTAs per edge, point-chunks ("units") per CTA
+  int max_iter;
+  int stage_pts;      // upc * chunk_pts
+  unsigned epoch;     // per-launch nonce (20 bits) of the partial all-gather flags
+};
+
+template <int KIND>
+__global__ void __launch_bounds__(kTrackThreads, 1)
+gn_track_kernel(const TrackArgs ta) {
+  const AccumArgs& a = ta.a;
+  extern __shared__ __align__(128) unsigned char dsm[];
+  __shared__ __align__(8) unsigned long long s_bar;
+  __shared__ EdgeXform s_X;
+  __shared__ float s_pose[(kSmallDim / 7 + 1) * 8];
+  __shared__ float s_warp[kTrackThreads / 32][kAcc];
+  __shared__ double s_part[8][kTrackMaxEdges * kAcc];
+  __shared__ double s_mvE[kTrackMaxEdges * kAcc];
+  __shared__ double s_G[kTrackThreads / 64][49];
+  __shared__ double s_TT[kTrackThreads / 64][49];
+  __shared__ double s_eb[kTrackMaxEdges * kEdgeBlock];
+  __shared__ int s_cnt[64];
+  __shared__ TrackGraph s_g;
+  __shared__ float s_dx[64];
+  __shared__ int s_flags[2];
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int E = a.e_local, n = a.n, N = a.ss.N;
+  const int e = blockIdx.x / ta.cpe, sub = blockIdx.x % ta.cpe;
+  const int i = a.ci[e], j = a.cj[e];
+  const int u_lo = min(sub * ta.upc, a.chunks), u_hi = min(a.chunks, u_lo + ta.upc);
+  const int nu = u_hi - u_lo;
+  if (a.ctrl[CTRL_DONE]) return;  // uniform over the grid: written before this launch
+#ifdef M3R_TRACK_PROF
+  long long trk_t = clock64();
+#endif
+
+  // shared-memory layout: per unit u a slab of chunk_pts points: Xj | rec | kloc | Xi
+  const uint32_t cp = (uint32_t)a.chunk_pts;
+  const uint32_t slab = cp * kTrackPtBytes;
+  const uint32_t off_rec = cp * 12u, off_k = cp * 20u, off_xi = cp * 22u;
+  double* solve_sm = reinterpret_cast<double*>(dsm + (size_t)ta.stage_pts * kTrackPtBytes);
+
+  if (tid < nu) s_cnt[tid] = a.counts[(size_t)e * a.chunks + u_lo + tid];
+  if (tid == 0) {
+    mbar_init(smem_u32(&s_bar), 1);
+    mbar_fence_init();
+  }
+  for (int t = tid; t < N * 8; t += kTrackThreads) s_pose[t] = a.Twc[t];
+  if (tid < E) {
+    s_g.ci[tid] = a.ci[tid];
+    s_g.cj[tid] = a.cj[tid];
+  }
+  if (tid >= 32 && tid < 32 + N + 1) s_g.inc_off[tid - 32] = a.ss.inc_off[tid - 32];
+  if (tid >= 64 && tid < 64 + 2 * E) s_g.inc_list[tid - 64] = a.ss.inc_list[tid - 64];
+  const int bad_ids = a.ctrl[CTRL_BAD];
+  __syncthreads();
+  if (tid == 0) {
+    const uint64_t pol = l2_policy_evict_first();
+    const uint32_t bar = smem_u32(&s_bar);
+    uint32_t total = 0;
+    for (int u = 0; u < nu; u++) {
+      const int cnt = s_cnt[u];
+      if (cnt <= 0) continue;
+      const int p_lo = (u_lo + u) * a.chunk_pts;
+      const int npts = min(n, p_lo + a.chunk_pts) - p_lo;
+      const uint32_t cnt8 = ((uint32_t)cnt + 7u) & ~7u;
+      total += (uint32_t)npts * 12u + cnt8 * 10u;
+    }
+    mbar_expect_tx(bar, total);
+    for (int u = 0; u < nu; u++) {
+      const int cnt = s_cnt[u];
+      if (cnt <= 0) continue;
+      const int p_lo = (u_lo + u) * a.chunk_pts;
+      const int npts = min(n, p_lo + a.chunk_pts) - p_lo;
+      const uint32_t cnt8 = ((uint32_t)cnt + 7u) & ~7u;
+      const uint32_t dst = smem_u32(dsm) + (uint32_t)u * slab;
+      bulk_g2s(dst, a.Xs + ((size_t)j * n + p_lo) * 3, (uint32_t)npts * 12u, bar, pol);
+      bulk_g2s(dst + off_rec, a.packed + (size_t)e * n + p_lo, cnt8 * 8u, bar, pol);
+      bulk_g2s(dst + off_k, a.kloc + (size_t)e * n + p_lo, cnt8 * 2u, bar, pol);
+    }
+  }
+  mbar_wait(smem_u32(&s_bar), 0);
+  // gather the matched points of frame i once (they do not depend on the poses)
+  {
+    const float* __restrict__ Xi = a.Xs + (size_t)i * n * 3;
+    for (int u = 0; u < nu; u++) {
+      const int cnt = s_cnt[u];
+      const uint2* srec = reinterpret_cast<const uint2*>(dsm + (size_t)u * slab + off_rec);
+      float* sxi = reinterpret_cast<float*>(dsm + (size_t)u * slab + off_xi);
+      for (int k = tid; k < cnt; k += kTrackThreads) {
+        const float* g = Xi + (size_t)srec[k].x * 3;
+        sxi[k * 3 + 0] = __ldg(g + 0);
+        sxi[k * 3 + 1] = __ldg(g + 1);
+        sxi[k * 3 + 2] = __ldg(g + 2);
+      }
+    }
+  }
+  TRK(0);  // staging + gather
+  AccumParams prm = a.prm;
+  if (KIND == M3R_GN_CALIB) {
+    prm.fx = __ldg(a.K + 0);
+    prm.fy = __ldg(a.K + 4);
+    prm.cx = __ldg(a.K + 2);
+    prm.cy = __ldg(a.K + 5);
+  }
+  const bool writer = blockIdx.x == 0;
+  const int pairs = E * kAcc;
+  int nslice = kTrackThreads / pairs;
+  nslice = nslice > 8 ? 8 : nslice;
+  int nfail = 0;
+
+  for (int it = 0; it < ta.max_iter; it++) {
+    if (tid == 0) edge_xform(s_pose + (size_t)i * 8, s_pose + (size_t)j * 8, s_X);
+    __syncthreads();  // s_X (and, first iteration, the gathered Xi)
+    TRK(1);  // edge xform
+    EdgeXform X;
+#pragma unroll
+    for (int t = 0; t < 9; t++) X.m[t] = s_X.m[t];
+#pragma unroll
+    for (int t = 0; t < 3; t++) X.t[t] = s_X.t[t];
+    float acc[kAcc];
+#pragma unroll
+    for (int t = 0; t < kAcc; t++) acc[t] = 0.f;
+    for (int u = 0; u < nu; u++) {
+      const int cnt = s_cnt[u];
+      const unsigned char* base = dsm + (size_t)u * slab;
+      const float* sx = reinterpret_cast<const float*>(base);
+      const uint2* srec = reinterpret_cast<const uint2*>(base + off_rec);
+      const uint16_t* sk = reinterpret_cast<const uint16_t*>(base + off_k);
+      const float* sxi = reinterpret_cast<const float*>(base + off_xi);
+      for (int k = tid; k < cnt; k += kTrackThreads) {
+        const uint2 rec = srec[k];
+        const float* xj = sx + (int)sk[k] * 3;
+        const float* xi = sxi + k * 3;
+        accum_point<KIND>(acc, X, prm, xj[0], xj[1], xj[2], __uint_as_float(rec.y), (int)rec.x, xi[0], xi[1], xi[2]);
+      }
+    }
+    TRK(2);  // accumulate
+    // CTA reduction (same transposing butterfly as gn_accum_kernel) -> fp64 partial of this CTA
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+      const bool up = (lane & off) != 0;
+#pragma unroll
+      for (int t = 0; t < off; t++) {
+        const float send = up ? acc[t] : acc[t + off];
+        const float keep = up ? acc[t + off] : acc[t];
+        acc[t] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+      }
+    }
+    s_warp[warp][lane] = acc[0];
+#pragma unroll
+    for (int t = 32; t < kAcc; t++) {
+      float v = acc[t];
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+      if (lane == 0) s_warp[warp][t] = v;
+    }
+    __syncthreads();
+    // All-gather of the per-CTA partials without a barrier (the NCCL "LL" idea): every fp64 partial is
+    // published as two 8-byte words {flag : 32 | half of the value : 32}; 8-byte stores are single-copy
+    // atomic, so a reader that sees this iteration's flag in a word also sees its payload and simply
+    // polls the words it needs.  One store + one L2 round trip replace [fence, atomic arrive, spin,
+    // load].  Two buffers alternate: a CTA can only be two iterations ahead of the slowest reader
+    // after that reader has consumed the older buffer.  The launch is cooperative (co-resident CTAs).
+    ulonglong2* ll = reinterpret_cast<ulonglong2*>(a.partials) + (size_t)(it & 1) * gridDim.x * kAcc;
+    const unsigned long long flag = ((unsigned long long)(ta.epoch << 12 | (unsigned)(it + 1))) << 32;
+    if (tid < kAcc) {
+      double s = 0.0;
+#pragma unroll
+      for (int wv = 0; wv < kTrackThreads / 32; wv++) s += (double)s_warp[wv][tid];
+      const unsigned long long bits = (unsigned long long)__double_as_longlong(s);
+      ulonglong2 w;
+      w.x = flag | (bits & 0xffffffffull);
+      w.y = flag | (bits >> 32);
+      asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(ll + (size_t)blockIdx.x * kAcc + tid), "l"(w.x),
+                   "l"(w.y)
+                   : "memory");
+    }
+    TRK(3);  // CTA reduction + partial store
+#ifdef M3R_TRACK_PROF
+    if (it == 5 && tid == 0) {
+      unsigned long long gt;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+      g_dbg[blockIdx.x] = gt;
+    }
+#endif
+    // the poses of this iteration travel back the same way: N*8 floats + the stop flag, one word each
+    unsigned long long* pose_ll = reinterpret_cast<unsigned long long*>(
+                                      reinterpret_cast<ulonglong2*>(a.partials) + (size_t)2 * gridDim.x * kAcc) +
+                                  (size_t)(it & 1) * 96;
+    if (!writer) {
+      // every other CTA just waits for the new poses (81 words at most, polled with a short back-off)
+      if (tid <= N * 8) {
+        unsigned long long wv;
+        while (true) {
+          asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(wv) : "l"(pose_ll + tid) : "memory");
+          if ((wv >> 32) == (flag >> 32)) break;
+          __nanosleep(64);
+        }
+        if (tid < N * 8) s_pose[tid] = __uint_as_float((unsigned)wv);
+        else s_flags[0] = (int)(unsigned)wv;
+      }
+#ifdef M3R_TRACK_PROF
+      if (it == 4 && tid == 0) {
+        unsigned long long gt;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+        g_dbg[300 + blockIdx.x] = gt;
+      }
+#endif
+      __syncthreads();
+      if (s_flags[0]) break;
+      __syncthreads();  // s_flags is rewritten by the next iteration
+      continue;
+    }
+    // CTA 0 (the solver): fixed-order sum of the cpe partials of each edge
+    if (tid < pairs * nslice) {
+      const int pr = tid % pairs, sl = tid / pairs;
+      const int ee = pr / kAcc, t = pr % kAcc;
+      const ulonglong2* p0 = ll + (size_t)ee * ta.cpe * kAcc + t;
+      double s = 0.0;
+      for (int c = sl; c < ta.cpe; c += 12 * nslice) {  // 12 polls in flight, summed in a fixed order
+        ulonglong2 w[12];
+        unsigned pending = 0;
+#pragma unroll
+        for (int q = 0; q < 12; q++)
+          if (c + q * nslice < ta.cpe) pending |= 1u << q;
+        while (pending) {
+#pragma unroll
+          for (int q = 0; q < 12; q++) {
+            if (pending & (1u << q))
+              asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];"
+                           : "=l"(w[q].x), "=l"(w[q].y)
+                           : "l"(p0 + (size_t)(c + q * nslice) * kAcc)
+                           : "memory");
+          }
+#pragma unroll
+          for (int q = 0; q < 12; q++) {
+            if ((pending & (1u << q)) && (w[q].x >> 32) == (flag >> 32) && (w[q].y >> 32) == (flag >> 32))
+              pending &= ~(1u << q);
+          }
+        }
+#pragma unroll
+        for (int q = 0; q < 12; q++) {
+          if (c + q * nslice < ta.cpe)
+            s += __longlong_as_double((long long)((w[q].x & 0xffffffffull) | (w[q].y << 32)));
+        }
+      }
+      s_part[sl][pr] = s;
+    }
+    TRK(4);  // all-gather
+#ifdef M3R_TRACK_PROF
+    if (it == 5 && tid == 0) {
+      unsigned long long gt;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+      g_dbg[600] = gt;
+    }
+#endif
+    __syncthreads();
+    if (tid < pairs) {
+      double s = s_part[0][tid];
+      for (int sl = 1; sl < nslice; sl++) s += s_part[sl][tid];
+      s_mvE[tid] = s;
+    }
+    __syncthreads();
+    TRK(5);  // partial sums
+    // adjoints: A_e = G^T M G, b_e = G^T v (groups of 64 threads, one edge each)
+    for (int e0 = 0; e0 < E; e0 += kTrackThreads / 64) {
+      const int grp = tid >> 6, lt = tid & 63, ee = e0 + grp;
+      const bool act = ee < E;
+      const double* mv = s_mvE + (act ? ee : 0) * kAcc;
+      if (act && lt < 7) {
+        const int m = lt;
+        const float* Ti = s_pose + (size_t)s_g.ci[ee] * 8;
+        const double tx = Ti[0], ty = Ti[1], tz = Ti[2], x = Ti[3], y = Ti[4], z = Ti[5], w = Ti[6];
+        const double s_inv = 1.0 / (double)Ti[7];
+        const double R[9] = {1 - 2 * (y * y + z * z), 2 * (x * y - z * w),     2 * (x * z + y * w),
+                             2 * (x * y + z * w),     1 - 2 * (x * x + z * z), 2 * (y * z - x * w),
+                             2 * (x * z - y * w),     2 * (y * z + x * w),     1 - 2 * (x * x + y * y)};
+        double row[7] = {0, 0, 0, 0, 0, 0, 0};
+        if (m < 3) {
+          const double c0 = R[0 + m], c1 = R[3 + m], c2 = R[6 + m];
+          row[0] = s_inv * c0; row[1] = s_inv * c1; row[2] = s_inv * c2;
+          row[3] = s_inv * (ty * c2 - tz * c1);
+          row[4] = s_inv * (tz * c0 - tx * c2);
+          row[5] = s_inv * (tx * c1 - ty * c0);
+          row[6] = s_inv * (tx * c0 + ty * c1 + tz * c2);
+        } else if (m < 6) {
+          row[3] = R[0 + (m - 3)]; row[4] = R[3 + (m - 3)]; row[5] = R[6 + (m - 3)];
+        } else {
+          row[6] = 1.0;
+        }
+#pragma unroll
+        for (int c = 0; c < 7; c++) s_G[grp][m * 7 + c] = row[c];
+      }
+      __syncthreads();
+      if (act && lt < 49) {
+        const int p = lt / 7, c = lt % 7;
+        double t = 0.0;
+#pragma unroll
+        for (int q = 0; q < 7; q++) t += ((p <= q) ? mv[tri(p, q)] : mv[tri(q, p)]) * s_G[grp][q * 7 + c];
+        s_TT[grp][lt] = t;
+      }
+      __syncthreads();
+      if (act && lt < 49) {
+        const int r = lt / 7, c = lt % 7;
+        double s = 0.0;
+#pragma unroll
+        for (int p = 0; p < 7; p++) s += s_G[grp][p * 7 + r] * s_TT[grp][p * 7 + c];
+        s_eb[ee * kEdgeBlock + lt] = s;
+      } else if (act && lt < 56) {
+        const int r = lt - 49;
+        double s = 0.0;
+#pragma unroll
+        for (int p = 0; p < 7; p++) s += s_G[grp][p * 7 + r] * mv[28 + p];
+        s_eb[ee * kEdgeBlock + lt] = s;
+      }
+      __syncthreads();
+    }
+    TRK(6);  // adjoints
+    track_solve(s_g, s_eb, s_pose, N, a.ss.dim, a.ss.delta_thresh, solve_sm, s_dx, s_flags);
+    TRK(7);  // solve + retraction
+    nfail += s_flags[1];
+    const int stop = s_flags[0];
+    {  // publish first (the other CTAs are waiting), then the plain stores of the outputs
+      if (tid <= N * 8) {
+        const unsigned payload = tid < N * 8 ? __float_as_uint(s_pose[tid]) : (unsigned)stop;
+        asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(pose_ll + tid), "l"(flag | (unsigned long long)payload)
+                     : "memory");
+      }
+#ifdef M3R_TRACK_PROF
+      if (it == 4 && tid == 0) {
+        unsigned long long gt;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
+        g_dbg[601] = gt;
+      }
+#endif
+      for (int t = tid; t < N * 8; t += kTrackThreads) a.ss.Twc[t] = s_pose[t];
+      for (int t = tid; t < a.ss.dim; t += kTrackThreads) a.ss.dx_out[t] = s_dx[t];
+      if (a.eb)
+        for (int t = tid; t < E * kEdgeBlock; t += kTrackThreads) a.eb[t] = s_eb[t];
+      if (tid == 0) {
+        a.ss.ctrl[CTRL_ITERS] = it + 1;
+        a.ss.ctrl[CTRL_FAILS] = nfail;
+        if (stop) {
+          a.ss.ctrl[CTRL_DONE] = 1;
+          a.ss.ctrl[CTRL_EARLY] = 1;
+        }
+        if (a.ss.info_out) {
+          a.ss.info_out[0] = it + 1;
+          a.ss.info_out[1] = nfail;
+          a.ss.info_out[2] = stop;
+          a.ss.info_out[3] = bad_ids;
+        }
+      }
+    }
+    if (stop) break;  // the other CTAs read the same flag from the published words
+    __syncthreads();   // s_flags / s_dx are rewritten by the next iteration
+  }
+}
+
+template <int KIND>
+int launch_track(const TrackArgs& ta, size_t dyn, cudaStream_t s) {
+  static bool attr_done = false;
+  if (!attr_done) {
+    M3R_CUDA_CHECK(cudaFuncSetAttribute(gn_track_kernel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        kTrackMaxPts * kTrackPtBytes + (int)small_solve_smem_bytes(kSmallDim)));
+    attr_done = true;
+  }
+  void* params[] = {const_cast<TrackArgs*>(&ta)};
+  M3R_CUDA_CHECK(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(gn_track_kernel<KIND>),
+                                             dim3(ta.a.e_local * ta.cpe), dim3(kTrackThreads), params, dyn, s));
+  return M3R_OK;
+}
+
 template <int KIND, bool STAGED>
 int launch_one(const AccumArgs& a, size_t dyn, bool pdl, cudaStream_t s) {
   cudaLaunchConfig_t cfg{};
@@ -686,12 +1059,12 @@ int launch_gn_pack(const float* Cs, const int64_t* idx, const uint8_t* valid, co
   return M3R_OK;
 }
 
-int launch_gn_accumulate(const float* Twc, const float* Xs, const float* K, const GnLayout& L, const GnPtrs& P,
-                         const m3r_gn_params& prm, int e_lo, int e_hi, const GnFuse& fuse, cudaStream_t s) {
+// AccumArgs shared by the per-iteration launch and the persistent tracking launch
+static int fill_accum_args(AccumArgs& a, bool& staged, size_t& dyn, const float* Twc, const float* Xs, const float* K,
+                           const GnLayout& L, const GnPtrs& P, const m3r_gn_params& prm, int e_lo, int e_hi,
+                           const GnFuse& fuse) {
   const int e_local = e_hi - e_lo;
-  if (e_local <= 0) return M3R_OK;
-  if (e_local > 65535 || e_local > L.edges_local) return M3R_ERR_UNSUPPORTED;
-  AccumArgs a{};
+  a = AccumArgs{};
   a.Twc = Twc; a.Xs = Xs; a.K = K; a.packed = P.packed;
   a.ci = P.ci; a.cj = P.cj; a.ctrl = P.ctrl; a.counters = P.counters; a.partials = P.partials; a.eb = P.eb;
   a.n = L.num_pts;
@@ -714,8 +1087,8 @@ int launch_gn_accumulate(const float* Twc, const float* Xs, const float* K, cons
   a.prm.v_hi = (float)(prm.height - 1 - prm.pixel_border);
   if (prm.kind == M3R_GN_CALIB && !K) return M3R_ERR_BAD_ARG;  // read on the device: the call stays asynchronous
   // TMA bulk copies need 16-byte aligned sources and sizes: n % 8 == 0 makes every chunk of all three streams so
-  const bool staged = (L.num_pts % 8 == 0) && (reinterpret_cast<uintptr_t>(Xs) % 16 == 0);
-  size_t dyn = staged ? (size_t)ck.chunk_pts * 22 : 0;
+  staged = (L.num_pts % 8 == 0) && (reinterpret_cast<uintptr_t>(Xs) % 16 == 0);
+  dyn = staged ? (size_t)ck.chunk_pts * 22 : 0;
   a.fuse = 0;
   if (fuse.enabled && L.dim <= kSmallDim && e_lo == 0 && e_hi == L.num_edges) {
     a.fuse = 1;
@@ -725,12 +1098,69 @@ int launch_gn_accumulate(const float* Twc, const float* Xs, const float* K, cons
     const size_t need = small_solve_smem_bytes(L.dim);
     if (need > dyn) dyn = need;
   }
+  return M3R_OK;
+}
+
+int launch_gn_accumulate(const float* Twc, const float* Xs, const float* K, const GnLayout& L, const GnPtrs& P,
+                         const m3r_gn_params& prm, int e_lo, int e_hi, const GnFuse& fuse, cudaStream_t s) {
+  const int e_local = e_hi - e_lo;
+  if (e_local <= 0) return M3R_OK;
+  if (e_local > 65535 || e_local > L.edges_local) return M3R_ERR_UNSUPPORTED;
+  AccumArgs a;
+  bool staged;
+  size_t dyn;
+  int rc = fill_accum_args(a, staged, dyn, Twc, Xs, K, L, P, prm, e_lo, e_hi, fuse);
+  if (rc != M3R_OK) return rc;
   switch (prm.kind) {
     case M3R_GN_POINTS: return launch_kind<M3R_GN_POINTS>(a, staged, dyn, fuse.pdl != 0, s);
     case M3R_GN_RAYS: return launch_kind<M3R_GN_RAYS>(a, staged, dyn, fuse.pdl != 0, s);
     case M3R_GN_CALIB: return launch_kind<M3R_GN_CALIB>(a, staged, dyn, fuse.pdl != 0, s);
     default: return M3R_ERR_BAD_ARG;
   }
+}
+
+// Whole GN loop in one cooperative launch (gn_track_kernel).  *launched = 0 when the problem is not
+// tracking-sized (the caller then runs the per-iteration path).
+int launch_gn_track(const float* Twc, const float* Xs, const float* K, const GnLayout& L, const GnPtrs& P,
+                    const m3r_gn_params& prm, const GnFuse& fuse, int* launched, cudaStream_t s) {
+  *launched = 0;
+  const int E = L.num_edges;
+  if (!fuse.enabled || E < 1 || E > kTrackMaxEdges || L.dim > kSmallDim || prm.max_iter < 1) return M3R_OK;
+  static int num_sms = 0, coop = 0;
+  if (num_sms == 0) {
+    int dev = 0;
+    M3R_CUDA_CHECK(cudaGetDevice(&dev));
+    M3R_CUDA_CHECK(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
+    M3R_CUDA_CHECK(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
+  }
+  if (!coop || num_sms < E) return M3R_OK;
+  AccumArgs a;
+  bool staged;
+  size_t dyn;
+  int rc = fill_accum_args(a, staged, dyn, Twc, Xs, K, L, P, prm, 0, E, fuse);
+  if (rc != M3R_OK) return rc;
+  if (!staged || !a.fuse) return M3R_OK;
+  TrackArgs ta{};
+  ta.a = a;
+  ta.cpe = std::min(a.chunks, num_sms / E);
+  ta.upc = (a.chunks + ta.cpe - 1) / ta.cpe;
+  ta.stage_pts = ta.upc * a.chunk_pts;
+  ta.max_iter = prm.max_iter;
+  if (ta.upc > 64 || ta.stage_pts > kTrackMaxPts || prm.max_iter > 4095) return M3R_OK;
+  // two gather buffers of grid x kAcc x 16 B + two pose buffers of 96 words live in P.partials
+  // (gn_layout reserves >= (4 * 148 + 8) x kAcc doubles)
+  if ((size_t)4 * E * ta.cpe + 8 > std::max((size_t)E * a.chunks, (size_t)4 * kNumSMs + 8)) return M3R_OK;
+  static std::atomic<unsigned> g_epoch{1};
+  ta.epoch = g_epoch.fetch_add(1) & 0xfffffu;
+  const size_t dyn_track = (size_t)ta.stage_pts * kTrackPtBytes + small_solve_smem_bytes(L.dim);
+  switch (prm.kind) {
+    case M3R_GN_POINTS: rc = launch_track<M3R_GN_POINTS>(ta, dyn_track, s); break;
+    case M3R_GN_RAYS: rc = launch_track<M3R_GN_RAYS>(ta, dyn_track, s); break;
+    case M3R_GN_CALIB: rc = launch_track<M3R_GN_CALIB>(ta, dyn_track, s); break;
+    default: return M3R_ERR_BAD_ARG;
+  }
+  if (rc == M3R_OK) *launched = 1;
+  return rc;
 }
 
 int launch_export_hs_gs(const GnLayout& L, const GnPtrs& P, float* Hs, float* gs, cudaStream_t s) {
@@ -741,3 +1171,9 @@ int launch_export_hs_gs(const GnLayout& L, const GnPtrs& P, float* Hs, float* gs
 }
 
 }  // namespace m3r
+
+#ifdef M3R_TRACK_PROF
+extern "C" int m3r_debug_read(void* out, size_t bytes) {
+  return (int)cudaMemcpyFromSymbol(out, m3r::g_dbg, bytes);
+}
+#endif

@@ -1,5 +1,7 @@
 // Workspace layout and shared declarations of the Gauss-Newton path (sm_100a).
 #pragma once
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace m3r {
@@ -79,7 +81,8 @@ inline GnLayout gn_layout(int num_kf, int num_edges, int num_pts, int edges_loca
   L.off_inc_off = take(sizeof(int) * ((size_t)num_kf + 1));
   L.off_inc_list = take(sizeof(int) * 2 * (size_t)num_edges);
   L.off_order = take(sizeof(int) * (size_t)num_edges);
-  const size_t worst = (size_t)num_edges * (size_t)gn_chunking(num_edges, num_pts).chunks;
+  // (the persistent tracking kernel keeps two all-gather buffers of 16 B x kAcc per CTA of a <= 148-CTA grid here)
+  const size_t worst = std::max((size_t)num_edges * (size_t)gn_chunking(num_edges, num_pts).chunks, (size_t)4 * kNumSMs + 8);
   L.off_partials = take(sizeof(double) * kAcc * worst);
   L.off_eb = take(sizeof(double) * kEdgeBlock * (size_t)num_edges);
   L.off_hd = take(sizeof(double) * (size_t)L.rows * L.ld);
@@ -151,6 +154,8 @@ int launch_gn_pack(const float* Cs, const int64_t* idx, const uint8_t* valid, co
                    const GnPtrs& P, const m3r_gn_params& prm, int e_lo, int e_hi, cudaStream_t s);
 int launch_gn_accumulate(const float* Twc, const float* Xs, const float* K, const GnLayout& L, const GnPtrs& P,
                          const m3r_gn_params& prm, int e_lo, int e_hi, const GnFuse& fuse, cudaStream_t s);
+int launch_gn_track(const float* Twc, const float* Xs, const float* K, const GnLayout& L, const GnPtrs& P,
+                    const m3r_gn_params& prm, const GnFuse& fuse, int* launched, cudaStream_t s);
 int launch_gn_solve(float* Twc, const GnLayout& L, const GnPtrs& P, float delta_thresh, float* dx_out,
                     int32_t* info_out, cudaStream_t s);
 int launch_export_hs_gs(const GnLayout& L, const GnPtrs& P, float* Hs, float* gs, cudaStream_t s);

@@ -114,7 +114,11 @@ __host__ __device__ inline size_t small_solve_smem_bytes(int dim) {
   return sizeof(double) * ((size_t)dim * (dim + 1) + 2 * (size_t)dim + 2);
 }
 
-__device__ inline void small_solve(const SmallSolveArgs& a, double* sm) {
+// LOCAL = true (persistent tracking kernel): every CTA of the grid runs the same solve on its own
+// shared-memory copies (a.eb and a.Twc point to shared memory); only the `writer` CTA touches the
+// global outputs (dx_out, ctrl, info_out), and the stop decision is returned through *stop_out (smem).
+template <bool LOCAL = false>
+__device__ inline void small_solve(const SmallSolveArgs& a, double* sm, bool writer = true, int* stop_out = nullptr) {
   const int tid = threadIdx.x, nt = blockDim.x;
   const int dim = a.dim, ld = dim + 1, nfree = a.N - 1;
   double* H = sm;                    // [dim][ld], lower triangle; H[j][j] keeps the raw pivot
@@ -133,7 +137,7 @@ __device__ inline void small_solve(const SmallSolveArgs& a, double* sm) {
       const int ent = a.inc_list[q];
       const int e = ent >> 1;
       const int other = ((ent & 1) ? a.ci[e] : a.cj[e]) - 1;
-      const double v = __ldcg(a.eb + (size_t)e * kEdgeBlock + rc);
+      const double v = LOCAL ? a.eb[(size_t)e * kEdgeBlock + rc] : __ldcg(a.eb + (size_t)e * kEdgeBlock + rc);
       diag += v;
       if (other >= 0 && other < p) H[(7 * p + r) * ld + 7 * other + c] -= v;
     }
@@ -144,7 +148,8 @@ __device__ inline void small_solve(const SmallSolveArgs& a, double* sm) {
     double g = 0.0;
     for (int q = a.inc_off[p + 1]; q < a.inc_off[p + 2]; q++) {
       const int ent = a.inc_list[q];
-      const double bv = __ldcg(a.eb + (size_t)(ent >> 1) * kEdgeBlock + 49 + k);
+      const double bv = LOCAL ? a.eb[(size_t)(ent >> 1) * kEdgeBlock + 49 + k]
+                              : __ldcg(a.eb + (size_t)(ent >> 1) * kEdgeBlock + 49 + k);
       g += (ent & 1) ? bv : -bv;  // g_i = -b_e, g_j = +b_e
     }
     x[t] = g;
@@ -192,7 +197,8 @@ __device__ inline void small_solve(const SmallSolveArgs& a, double* sm) {
   }
   __syncthreads();
   const bool failed = *s_fail != 0;  // non-SPD => dx = 0 (gn_kernels.cu:147-150)
-  for (int t = tid; t < dim; t += nt) a.dx_out[t] = failed ? 0.0f : (float)(-x[t]);
+  if (writer)
+    for (int t = tid; t < dim; t += nt) a.dx_out[t] = failed ? 0.0f : (float)(-x[t]);
   for (int k = 1 + tid; k < a.N; k += nt) {
     float T[8], xi[7];
 #pragma unroll
@@ -210,6 +216,8 @@ __device__ inline void small_solve(const SmallSolveArgs& a, double* sm) {
       tot += (double)d * (double)d;
     }
     const float nrm = (float)sqrt(tot);
+    if (LOCAL) *stop_out = (nrm < a.delta_thresh) ? 1 : 0;
+    if (!writer) return;
     a.ctrl[CTRL_ITERS] += 1;
     if (failed) a.ctrl[CTRL_FAILS] += 1;
     if (nrm < a.delta_thresh) {
@@ -223,6 +231,186 @@ __device__ inline void small_solve(const SmallSolveArgs& a, double* sm) {
       a.info_out[3] = a.ctrl[CTRL_BAD];
     }
   }
+}
+
+// One free pose (frame-to-keyframe tracking): the whole factorisation fits in the registers of one
+// thread and is fully unrolled -- no shared-memory round trips or warp barriers on the dependency
+// chain.  Not inlined: it gets its own register allocation instead of spilling next to the
+// accumulators of the calling kernel.
+static __device__ __noinline__ void track_solve7(const double* H, const double* x, int ld, float* pose, float delta_thresh,
+                                          float* dx_sm, int* flags) {
+  double L[28], y[7];
+#pragma unroll
+  for (int r = 0; r < 7; r++) {
+#pragma unroll
+    for (int c = 0; c <= r; c++) L[r * (r + 1) / 2 + c] = H[r * ld + c];
+    y[r] = x[r];
+  }
+  bool failed = false;
+  double inv[7];
+#pragma unroll
+  for (int j = 0; j < 7; j++) {
+    double d = L[j * (j + 1) / 2 + j];
+#pragma unroll
+    for (int k = 0; k < j; k++) d -= L[j * (j + 1) / 2 + k] * L[j * (j + 1) / 2 + k];
+    if (!(d > 0.0)) {
+      d = 1.0;
+      failed = true;
+    }
+    inv[j] = rsqrt(d);
+#pragma unroll
+    for (int r = j + 1; r < 7; r++) {
+      double v = L[r * (r + 1) / 2 + j];
+#pragma unroll
+      for (int k = 0; k < j; k++) v -= L[r * (r + 1) / 2 + k] * L[j * (j + 1) / 2 + k];
+      L[r * (r + 1) / 2 + j] = v * inv[j];
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 7; j++) {
+#pragma unroll
+    for (int k = 0; k < j; k++) y[j] -= L[j * (j + 1) / 2 + k] * y[k];
+    y[j] *= inv[j];
+  }
+#pragma unroll
+  for (int j = 6; j >= 0; j--) {
+#pragma unroll
+    for (int k = j + 1; k < 7; k++) y[j] -= L[k * (k + 1) / 2 + j] * y[k];
+    y[j] *= inv[j];
+  }
+  float xi[7], T[8];
+  double tot = 0.0;
+#pragma unroll
+  for (int c = 0; c < 7; c++) {
+    xi[c] = failed ? 0.0f : (float)(-y[c]);
+    dx_sm[c] = xi[c];
+    tot += (double)xi[c] * (double)xi[c];
+  }
+#pragma unroll
+  for (int c = 0; c < 8; c++) T[c] = pose[8 + c];
+  sim3_retract(xi, T);
+#pragma unroll
+  for (int c = 0; c < 8; c++) pose[8 + c] = T[c];
+  flags[0] = ((float)sqrt(tot) < delta_thresh) ? 1 : 0;
+  flags[1] = failed ? 1 : 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Solve of the persistent tracking kernel: same mathematics as small_solve, laid out for latency.
+// Everything it reads lives in shared memory (edge blocks, poses, the cached graph structure), the
+// Cholesky / substitutions / retraction run in warp 0 with __syncwarp only (lanes own rows lane and
+// lane + 32; reciprocals of the pivots' roots are kept so the substitutions multiply), and nothing is
+// read from global memory.  Called by ALL threads of the CTA; ends with a __syncthreads.
+struct TrackGraph {      // shared-memory copy of what gn_prepare produced (E <= 8, N <= 10)
+  int ci[8], cj[8];
+  int inc_off[12];
+  int inc_list[16];
+};
+
+// returns (in *flags, shared): flags[0] = stop (|dx| < delta_thresh), flags[1] = factorisation failed
+__device__ inline void track_solve(const TrackGraph& g, const double* eb, float* pose, int N, int dim,
+                                   float delta_thresh, double* sm, float* dx_sm, int* flags) {
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const int ld = dim + 1, nfree = N - 1;
+  double* H = sm;                     // [dim][ld] lower triangle
+  double* x = sm + (size_t)dim * ld;  // rhs / solution
+  double* dinv = x + dim;             // 1 / sqrt(pivot)
+  // assemble: every (pose p, r, c) entry of the block lower triangle is owned by one thread
+  for (int t = tid; t < nfree * nfree * 49; t += nt) {
+    const int blk = t / 49, rc = t % 49, r = rc / 7, c = rc % 7;
+    const int p = blk / nfree, o = blk % nfree;
+    if (o > p) continue;
+    double v = 0.0;
+    for (int q = g.inc_off[p + 1]; q < g.inc_off[p + 2]; q++) {
+      const int ent = g.inc_list[q];
+      const int e = ent >> 1;
+      const int other = ((ent & 1) ? g.ci[e] : g.cj[e]) - 1;
+      const double b = eb[e * kEdgeBlock + rc];
+      if (o == p) v += b;
+      else if (other == o) v -= b;
+    }
+    H[(7 * p + r) * ld + 7 * o + c] = v;
+  }
+  for (int t = tid; t < dim; t += nt) {
+    const int p = t / 7, k = t % 7;
+    double gsum = 0.0;
+    for (int q = g.inc_off[p + 1]; q < g.inc_off[p + 2]; q++) {
+      const int ent = g.inc_list[q];
+      const double bv = eb[(ent >> 1) * kEdgeBlock + 49 + k];
+      gsum += (ent & 1) ? bv : -bv;  // g_i = -b_e, g_j = +b_e
+    }
+    x[t] = gsum;
+  }
+  __syncthreads();
+  if (dim == 7) {
+    if (tid == 0) track_solve7(H, x, ld, pose, delta_thresh, dx_sm, flags);
+  } else if (tid < 32) {
+    const int lane = tid;
+    const int r0 = lane, r1 = lane + 32;
+    bool failed = false;
+    for (int j = 0; j < dim; j++) {
+      double s0 = 0.0, s1 = 0.0;
+      if (r0 >= j && r0 < dim) {
+        s0 = H[r0 * ld + j];
+        for (int k = 0; k < j; k++) s0 -= H[r0 * ld + k] * H[j * ld + k];
+      }
+      if (r1 >= j && r1 < dim) {
+        s1 = H[r1 * ld + j];
+        for (int k = 0; k < j; k++) s1 -= H[r1 * ld + k] * H[j * ld + k];
+      }
+      double d = __shfl_sync(0xffffffffu, j < 32 ? s0 : s1, j & 31);
+      if (!(d > 0.0)) {  // non-SPD => dx = 0 (gn_kernels.cu:147-150)
+        d = 1.0;
+        failed = true;
+      }
+      const double inv = 1.0 / sqrt(d);
+      if (r0 > j && r0 < dim) H[r0 * ld + j] = s0 * inv;
+      if (r1 > j && r1 < dim) H[r1 * ld + j] = s1 * inv;
+      if (lane == 0) dinv[j] = inv;
+      __syncwarp();
+    }
+    // L y = g, then L^T x = y
+    for (int j = 0; j < dim; j++) {
+      const double yj = x[j] * dinv[j];
+      __syncwarp();
+      if (lane == 0) x[j] = yj;
+      if (r0 > j && r0 < dim) x[r0] -= H[r0 * ld + j] * yj;
+      if (r1 > j && r1 < dim) x[r1] -= H[r1 * ld + j] * yj;
+      __syncwarp();
+    }
+    for (int j = dim - 1; j >= 0; j--) {
+      const double xj = x[j] * dinv[j];
+      __syncwarp();
+      if (lane == 0) x[j] = xj;
+      if (r0 < j) x[r0] -= H[j * ld + r0] * xj;
+      if (r1 < j) x[r1] -= H[j * ld + r1] * xj;
+      __syncwarp();
+    }
+    float d0 = 0.f, d1 = 0.f;
+    if (r0 < dim) d0 = failed ? 0.0f : (float)(-x[r0]);
+    if (r1 < dim) d1 = failed ? 0.0f : (float)(-x[r1]);
+    if (r0 < dim) dx_sm[r0] = d0;
+    if (r1 < dim) dx_sm[r1] = d1;
+    double tot = (double)d0 * (double)d0 + (double)d1 * (double)d1;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, off);
+    __syncwarp();
+    if (lane >= 1 && lane < N) {
+      float T[8], xi[7];
+#pragma unroll
+      for (int c = 0; c < 8; c++) T[c] = pose[lane * 8 + c];
+#pragma unroll
+      for (int c = 0; c < 7; c++) xi[c] = dx_sm[(lane - 1) * 7 + c];
+      sim3_retract(xi, T);
+#pragma unroll
+      for (int c = 0; c < 8; c++) pose[lane * 8 + c] = T[c];
+    }
+    if (lane == 0) {
+      flags[0] = ((float)sqrt(tot) < delta_thresh) ? 1 : 0;
+      flags[1] = failed ? 1 : 0;
+    }
+  }
+  __syncthreads();
 }
 
 }  // namespace m3r

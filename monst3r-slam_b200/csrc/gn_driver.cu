@@ -233,6 +233,13 @@ extern "C" int m3r_gauss_newton(float* Twc, const float* Xs, const float* Cs, co
     rc = launch_gn_pack(Cs, idx, valid, Q, L, P, *params, lo, hi, s);
     if (rc != M3R_OK) return rc;
   }
+  if (params->max_iter > 0 && fuse.enabled) {
+    // tracking-sized: the whole loop is one cooperative launch (gn_track_kernel)
+    int launched = 0;
+    rc = launch_gn_track(Twc, Xs, K, L, P, *params, fuse, &launched, s);
+    if (rc != M3R_OK) return rc;
+    if (launched) return M3R_OK;
+  }
   for (int it = 0; it < params->max_iter; it++) {
     fuse.pdl = fuse.enabled && it > 0;  // iteration 0 follows pack: full serialisation
     rc = accumulate_step(Twc, Xs, K, L, P, *params, shard, lo, hi, fuse, s);
