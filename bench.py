@@ -101,6 +101,25 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def ncu_traffic(kernel_name):
+    """dram__bytes_read + dram__bytes_write per launch of `kernel_name`, from the committed `ncu --set full`
+    summary of the same step (profiles/*_ncu_full_summary.csv, newest first); None if not captured."""
+    import csv
+    import glob
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "*_ncu_full_summary.csv")), reverse=True):
+        try:
+            rows = list(csv.reader(open(path)))
+            hdr, units = rows[0], rows[1]
+            ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+            scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+            for r in rows[2:]:
+                if kernel_name.split("(")[0].strip() in r[0]:
+                    return float(r[ir]) * scale.get(units[ir], 1.0) + float(r[iw]) * scale.get(units[iw], 1.0)
+        except (OSError, ValueError, IndexError):
+            continue
+    return None
+
+
 def load_pkg():
     pkg = importlib.import_module("monst3r-slam_b200")
     return (pkg, importlib.import_module("monst3r-slam_b200.abi"), importlib.import_module("monst3r-slam_b200.synth"),
@@ -200,8 +219,8 @@ def run_gpu(args):
     total_ms = max_over_ranks(sum(ts))
     ms_per_step = total_ms / K
     value = world * N_PX / (ms_per_step * 1e-3)
-    # iter_proj, refine, gn_prepare, gn_pack, 10 x gn_accum (the small solve + retraction ride in its last CTA)
-    launches_per_step = 1 + 1 + 1 + 1 + GN_RAYS["max_iter"]
+    # iter_proj, refine_staged, gn_prepare, gn_pack, gn_track (one cooperative launch runs all GN iterations)
+    launches_per_step = 1 + 1 + 1 + 1 + 1
 
     # ---- per-kernel timings for the roofline (rank 0 numbers; kernels timed alone, cold L2) -------
     peak, peak_kind = peaks()
@@ -237,11 +256,11 @@ def run_gpu(args):
 
     reps = max(K, 10)
     for name, fn, nbytes, per_step in (("iter_proj_kernel", k_iter, BYTES_ITER_PROJ * N_PX, 1),
-                                       ("refine_f16_fd24_kernel", k_refine, BYTES_REFINE * N_PX, 1),
+                                       ("refine_staged_kernel", k_refine, BYTES_REFINE * N_PX, 1),
                                        ("gn_pack_kernel (inside gauss_newton)", k_pack, (13 + 8) * E2 * n + 8 * N * n, 0),
                                        ("gn_accum_kernel<rays> (accumulate only, cold L2)", k_accum, gn_bytes(E2, N), 0),
                                        ("gn_small_solve_kernel (stand-alone)", k_solve, 0, 0),
-                                       ("gauss_newton_rays x10 (prepare + pack + 10 fused accumulate/solve launches)",
+                                       ("gauss_newton_rays x10 (gn_prepare + gn_pack + persistent gn_track_kernel)",
                                         k_gn, gn_bytes(E2, N) * GN_RAYS["max_iter"], 1)):
         t = timed(fn, reps, 3)
         ms = statistics.median(t)
@@ -253,7 +272,7 @@ def run_gpu(args):
     abi.gn_pack(prm, inp["Cs"], inp["idx"], inp["valid"], inp["Q"], N, E2, ws)
     dom = max(kern, key=lambda k_: kern[k_]["share_of_step"] if kern[k_]["bytes"] else -1)
     roofline = {"kernel": dom, "bound": "hbm", "achieved": kern[dom]["GBps"], "peak": peak, "unit": "GB/s",
-                "frac": kern[dom]["frac_of_hbm_peak"], "traffic": None, "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs)",
+                "frac": kern[dom]["frac_of_hbm_peak"], "traffic": ncu_traffic(dom), "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs)",
                 "note": "algorithmic bytes / CUDA-event time of the kernel launched alone with a cold L2; "
                         "time-bound by instruction issue / L1 gathers, not HBM (see DESIGN.md, profiles/)"}
 
@@ -273,17 +292,17 @@ def run_gpu(args):
     groups = (("rays", "pts", "p0"), ("D11", "D21"), ("Twc0", "Xs", "Cs", "ii", "jj", "idx", "valid", "Q"))
     assert sorted(k for g_ in groups for k in g_) == sorted(host.keys())
 
+    dv = {k: torch.empty_like(v, device=dev) for k, v in host.items()}  # device staging buffers, allocated once
+
     def step_e2e():
         cur = torch.cuda.current_stream(dev)
         s_up.wait_stream(cur)  # nothing starts before the timed region opens
-        dv, ready = {}, []
+        ready = []
         with torch.cuda.stream(s_up):
             for g_ in groups:
                 for k_ in g_:
-                    dv[k_] = host[k_].to(dev, non_blocking=True)
+                    dv[k_].copy_(host[k_], non_blocking=True)
                 ready.append(s_up.record_event())
-        for t_ in dv.values():
-            t_.record_stream(cur)
         cur.wait_event(ready[0])
         p, conv = ops.iter_proj(dv["rays"], dv["pts"], dv["p0"], MATCH_CFG["max_iter"], MATCH_CFG["lambda_init"],
                                 MATCH_CFG["convergence_thresh"])
