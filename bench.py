@@ -101,6 +101,15 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+_REAL_STDOUT = None
+
+
+def emit(line):
+    out = _REAL_STDOUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def ncu_traffic(kernel_name):
     """dram__bytes_read + dram__bytes_write per launch of `kernel_name`, from the committed `ncu --set full`
     summary of the same step (profiles/*_ncu_full_summary.csv, newest first); None if not captured."""
@@ -219,8 +228,9 @@ def run_gpu(args):
     total_ms = max_over_ranks(sum(ts))
     ms_per_step = total_ms / K
     value = world * N_PX / (ms_per_step * 1e-3)
-    # iter_proj, refine_staged, gn_prepare, gn_pack, gn_track (one cooperative launch runs all GN iterations)
-    launches_per_step = 1 + 1 + 1 + 1 + 1
+    # iter_proj_repack, iter_proj_padded, refine_staged, gn_prepare, gn_pack, gn_track (one cooperative launch
+    # runs all GN iterations)
+    launches_per_step = 2 + 1 + 1 + 1 + 1
 
     # ---- per-kernel timings for the roofline (rank 0 numbers; kernels timed alone, cold L2) -------
     peak, peak_kind = peaks()
@@ -255,7 +265,7 @@ def run_gpu(args):
                                      abi._ptr(ws), abi.C.c_size_t(ws.numel()), abi._stream())
 
     reps = max(K, 10)
-    for name, fn, nbytes, per_step in (("iter_proj_kernel", k_iter, BYTES_ITER_PROJ * N_PX, 1),
+    for name, fn, nbytes, per_step in (("iter_proj (iter_proj_repack_kernel + iter_proj_padded_kernel)", k_iter, BYTES_ITER_PROJ * N_PX, 1),
                                        ("refine_staged_kernel", k_refine, BYTES_REFINE * N_PX, 1),
                                        ("gn_pack_kernel (inside gauss_newton)", k_pack, (13 + 8) * E2 * n + 8 * N * n, 0),
                                        ("gn_accum_kernel<rays> (accumulate only, cold L2)", k_accum, gn_bytes(E2, N), 0),
@@ -352,7 +362,7 @@ def run_gpu(args):
                            "parallelism": f"replicas x{world}" if world > 1 else "1 GPU"},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * K,
                 "roofline": roofline, "kernels": kern, "cpu_baseline": cpu, "global_opt": gopt}
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -527,7 +537,7 @@ def run_reference(args):
             "cpu_baseline": cpu,
             "e2e": {"value": cpu["value"], "unit": "px/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line))
+    emit(line)
 
 
 def main():
@@ -539,6 +549,12 @@ def main():
     ap.add_argument("--global-opt", default="c3", choices=["c3", "c4", "none"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    # stdout carries exactly ONE JSON line: anything a library prints on fd 1 meanwhile (NCCL's version banner,
+    # torchrun notices) is sent to stderr, and the line is written to the real stdout at the end.
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -58,6 +58,14 @@ int m3r_iter_proj(const float* rays_img, const float* pts3d_norm, const float* p
                   float* p_new, uint8_t* converged, int b, int h, int w, int n, int max_iter,
                   float lambda_init, float cost_thresh, void* stream);
 
+/* Same op with a caller-provided scratch buffer of m3r_iter_proj_workspace_bytes(b,h,w) bytes
+ * (16-byte aligned): the ray image is first re-packed to 48-byte texels so that every bilinear tap is
+ * a 128-bit load.  Results are identical to m3r_iter_proj; workspace == NULL falls back to it. */
+size_t m3r_iter_proj_workspace_bytes(int b, int h, int w);
+int m3r_iter_proj_ws(const float* rays_img, const float* pts3d_norm, const float* p_init, float* p_new,
+                     uint8_t* converged, int b, int h, int w, int n, int max_iter, float lambda_init,
+                     float cost_thresh, void* workspace, size_t workspace_bytes, void* stream);
+
 /* refine_matches: D11 [b,h,w,fdim], D21 [b,n,fdim], p1 [b,n,2] i64 (u,v) -> p1_new [b,n,2] i64.
  * The f16 variant reproduces c10::Half arithmetic (every * and + rounded to fp16, k ascending,
  * best score starts at 0); f32/f64 start at FLT_MIN/DBL_MIN like the reference template. */

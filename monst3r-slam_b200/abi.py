@@ -19,7 +19,8 @@ GN_POINTS, GN_RAYS, GN_CALIB = 0, 1, 2
 MAX_KF_ID = 1 << 20
 
 EXPORTS = [
-    "m3r_abi_version", "m3r_last_error", "m3r_iter_proj", "m3r_refine_matches_f16",
+    "m3r_abi_version", "m3r_last_error", "m3r_iter_proj", "m3r_iter_proj_ws", "m3r_iter_proj_workspace_bytes",
+    "m3r_refine_matches_f16",
     "m3r_refine_matches_f32", "m3r_refine_matches_f64", "m3r_gn_workspace_bytes", "m3r_gn_workspace_bytes_sharded",
     "m3r_gauss_newton", "m3r_gn_prepare", "m3r_gn_pack", "m3r_gn_accumulate", "m3r_gn_edge_blocks", "m3r_gn_solve_retract",
     "m3r_gn_export_hs_gs", "m3r_pose_retr", "m3r_comm_unique_id", "m3r_comm_init", "m3r_comm_destroy",
@@ -45,6 +46,8 @@ def _load():
             "(there is no CPU or PyTorch fallback for this backend)")
     lib = C.CDLL(LIB_PATH)
     lib.m3r_last_error.restype = C.c_char_p
+    lib.m3r_iter_proj_workspace_bytes.restype = C.c_size_t
+    lib.m3r_iter_proj_workspace_bytes.argtypes = [C.c_int, C.c_int, C.c_int]
     lib.m3r_gn_workspace_bytes.restype = C.c_size_t
     lib.m3r_gn_workspace_bytes.argtypes = [C.c_int, C.c_int, C.c_int]
     lib.m3r_gn_workspace_bytes_sharded.restype = C.c_size_t
@@ -81,7 +84,8 @@ def _req(t, name, dtype=None):
         raise M3RError(f"{name} must be {dtype}, got {t.dtype}")
 
 
-def iter_proj(rays_img_with_grad, pts_3d_norm, p_init, max_iter, lambda_init, cost_thresh):
+def iter_proj(rays_img_with_grad, pts_3d_norm, p_init, max_iter, lambda_init, cost_thresh, padded=True):
+    """padded=True: m3r_iter_proj_ws (48-byte texels in a scratch buffer); False: the plain kernel."""
     for t, nm in ((rays_img_with_grad, "rays_img_with_grad"), (pts_3d_norm, "pts_3d_norm"), (p_init, "p_init")):
         _req(t, nm, torch.float32)
     b, h, w, c = rays_img_with_grad.shape
@@ -89,9 +93,17 @@ def iter_proj(rays_img_with_grad, pts_3d_norm, p_init, max_iter, lambda_init, co
     n = p_init.shape[1]
     p_new = torch.empty((b, n, 2), dtype=torch.float32, device=p_init.device)
     conv = torch.empty((b, n), dtype=torch.bool, device=p_init.device)
-    _check(lib.m3r_iter_proj(_ptr(rays_img_with_grad), _ptr(pts_3d_norm), _ptr(p_init), _ptr(p_new),
-                             _ptr(conv), b, h, w, n, int(max_iter), C.c_float(lambda_init),
-                             C.c_float(cost_thresh), _stream()), "m3r_iter_proj")
+    if padded:
+        nbytes = int(lib.m3r_iter_proj_workspace_bytes(b, h, w))
+        ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=p_init.device)
+        _check(lib.m3r_iter_proj_ws(_ptr(rays_img_with_grad), _ptr(pts_3d_norm), _ptr(p_init), _ptr(p_new),
+                                    _ptr(conv), b, h, w, n, int(max_iter), C.c_float(lambda_init),
+                                    C.c_float(cost_thresh), _ptr(ws), C.c_size_t(nbytes), _stream()),
+               "m3r_iter_proj_ws")
+    else:
+        _check(lib.m3r_iter_proj(_ptr(rays_img_with_grad), _ptr(pts_3d_norm), _ptr(p_init), _ptr(p_new),
+                                 _ptr(conv), b, h, w, n, int(max_iter), C.c_float(lambda_init),
+                                 C.c_float(cost_thresh), _stream()), "m3r_iter_proj")
     return [p_new, conv]
 
 

@@ -46,6 +46,23 @@ def test_iter_proj_vs_reference_cuda_full_size(backends, ref_backends, synth, b)
     assert (c == cr).float().mean().item() >= 0.999
 
 
+def test_iter_proj_padded_equals_plain_kernel(abi, synth):
+    """the 48-byte-texel path (m3r_iter_proj_ws) and the plain kernel run the same arithmetic on the same
+    values (only the compiler's FMA contraction may differ): identical pixels and flags, sub-1e-4 px floats;
+    identity and previous-frame inits, batch 2, ragged n (scalar tail of the re-pack)"""
+    need_gpu()
+    for init, n, hw in (("identity", None, (96, 128)), ("previous", None, (96, 128)), ("identity", 1001, (96, 128)),
+                        ("identity", None, (37, 53))):
+        d, rays, pts, p0 = _prep(synth, hw[0], hw[1], 33, b=2, init=init)
+        if n:
+            pts, p0 = pts[:, :n].contiguous(), p0[:, :n].contiguous()
+        a = abi.iter_proj(rays, pts, p0, 10, 1e-8, 1e-6, padded=True)
+        c = abi.iter_proj(rays, pts, p0, 10, 1e-8, 1e-6, padded=False)
+        assert torch.equal(a[0].long(), c[0].long()) and torch.equal(a[1], c[1])
+        assert (a[0] - c[0]).abs().max().item() < 1e-4
+        assert (a[0] != c[0]).any(-1).float().mean().item() < 1e-2
+
+
 def test_iter_proj_ragged_n_and_zero_iter(backends, oracle, synth):
     need_gpu()
     d, rays, pts, p0 = _prep(synth, 48, 64, 5)

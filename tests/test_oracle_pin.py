@@ -136,3 +136,18 @@ def test_golden_gn(oracle):
             int(g["pixel_border"]), float(g["z_eps"]))
         rel, ang = pose_diff(Twc, g["Twc_ref"])
         assert rel < 1e-5 and ang < 1e-4, (f, rel, ang)
+
+
+def test_double_reciprocal_rounded_to_float_equals_float_division():
+    """iter_proj.cu replaces the reference's `float y = 1.0 / x` (double divide, rounded to float) by the IEEE
+    single-precision division: double rounding is innocuous for division when the wide format has >= 2p+2
+    digits.  Checked here on 20 M random bit patterns plus the special values."""
+    rng = np.random.default_rng(7)
+    bits = rng.integers(0, 2 ** 32, size=20_000_000, dtype=np.uint64).astype(np.uint32)
+    x = np.concatenate([bits.view(np.float32), np.array([0.0, -0.0, np.inf, -np.inf, np.nan, 1e-45, -1e-45, 1.1754944e-38,
+                                                         3.4028235e38, 1.0, 3.0, 1e-6, 0.99999994], dtype=np.float32)])
+    with np.errstate(all="ignore"):
+        a = (1.0 / x.astype(np.float64)).astype(np.float32)
+        b = np.float32(1.0) / x
+    same = (a.view(np.uint32) == b.view(np.uint32)) | (np.isnan(a) & np.isnan(b))
+    assert same.all(), x[~same][:10]
