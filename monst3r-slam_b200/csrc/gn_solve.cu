@@ -21,6 +21,8 @@
 //      following :299-413, ||dx|| stop test, next-iteration bookkeeping.
 #include <cooperative_groups.h>
 
+#include <cstdlib>
+
 #include "gn_device.cuh"
 
 namespace cg = cooperative_groups;
@@ -254,7 +256,7 @@ __device__ bool tile_potrf_invert(double (*Ls)[kTile + 1], double (*Li)[kTile + 
 }
 
 template <bool COOP>
-__global__ void __launch_bounds__(kSolveThreads)
+__global__ void __launch_bounds__(kSolveThreads, 2)
 gn_solve_kernel(const SolveArgs a) {
   if (a.ctrl[CTRL_DONE]) return;  // uniform over the grid: set only by a previous launch
   __shared__ double sA[kTile][kTile + 1];
@@ -319,6 +321,12 @@ gn_solve_kernel(const SolveArgs a) {
   }
   grid_barrier<COOP>();
 
+#ifdef M3R_TRACK_PROF
+  long long trk_t = clock64();
+#define SLV(slot) do { if (blockIdx.x == 0 && tid == 0) { const long long n_ = clock64(); a.ctrl[6 + (slot)] += (int)((n_ - trk_t) >> 4); trk_t = n_; } } while (0)
+#else
+#define SLV(slot) do { } while (0)
+#endif
   // ---------------------------------------------------------------- B. Cholesky
   bool failed = false;
   for (int kb = 0; kb < nblk; kb++) {
@@ -329,6 +337,7 @@ gn_solve_kernel(const SolveArgs a) {
     }
     __syncthreads();
     if (!tile_potrf_invert(sA, sB, s_dinv, &s_flag)) failed = true;  // sA = L_kk, sB = L_kk^-1
+    SLV(0);
     if (blockIdx.x == 0) {
       for (int t = tid; t < kTile * kTile; t += kSolveThreads) {
         const int r = t >> 5, c = t & 31;
@@ -349,7 +358,9 @@ gn_solve_kernel(const SolveArgs a) {
         H[(size_t)(I * kTile + r) * ld + kb * kTile + c] = s;
       }
     }
+    SLV(1);
     grid_barrier<COOP>();
+    SLV(2);
     // B2: trailing update  A_IJ -= L_Ik * L_Jk^T  for kb < J <= I <= nblk (J < nblk)
     const int rem = nblk - kb;          // tile rows below kb, including the rhs row
     const int ncols = rem - 1;          // tile columns kb+1 .. nblk-1
@@ -391,7 +402,9 @@ gn_solve_kernel(const SolveArgs a) {
         o[(size_t)(r + 16) * ld + c + 16] = __ldcg(&o[(size_t)(r + 16) * ld + c + 16]) - acc11;
       }
     }
+    SLV(3);
     grid_barrier<COOP>();
+    SLV(4);
   }
   if (blockIdx.x != 0) return;
 
@@ -418,6 +431,7 @@ gn_solve_kernel(const SolveArgs a) {
     __syncthreads();
   }
 
+  SLV(5);
   // ---------------------------------------------------------------- D. dx, retraction, stop test
   double ss = 0.0;
   for (int t = tid; t < dim; t += kSolveThreads) {
@@ -503,7 +517,9 @@ int launch_gn_solve(float* Twc, const GnLayout& L, const GnPtrs& P, float delta_
     M3R_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     M3R_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gn_solve_kernel<true>, kSolveThreads, dyn));
     if (per_sm < 1) return M3R_ERR_UNSUPPORTED;
-    g_coop_grid = sms;  // one CTA per SM: the grid barrier cost grows with the CTA count
+    // two CTAs per SM: the trailing update is bound by the latency of its tile loads, a second CTA hides some
+    // of it (measured at dim 1785: 1.98 -> 1.87 ms per solve); more only makes the grid barriers dearer
+    g_coop_grid = sms * (per_sm >= 2 ? 2 : 1);
   }
   int grid = g_coop_grid;
   const int max_useful = L.nblk * (L.nblk + 1) / 2 + L.nblk;
