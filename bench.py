@@ -341,6 +341,22 @@ def run_gpu(args):
            "api": "mast3r_slam_backends.iter_proj / refine_matches / gauss_newton_rays (pybind drop-in), pinned host "
                   "buffers; H2D on a copy stream in op order, each op waits only for its own inputs, D2H on a third stream"}
 
+    # ---- matching.match(): torch glue around the two ops vs the fused path, rank 0 numbers ---
+    d_raw = synth.make_matching_pair(H, W, seed=1001 + 10 * rank, device=dev)
+
+    def m_glue():
+        matching.match(d_raw["X11"], d_raw["X21"], d_raw["D11"], d_raw["D21"], None, ops=ops)
+
+    def m_fused():
+        ops.match_fused(d_raw["X11"], d_raw["X21"], d_raw["D11"], d_raw["D21"].view(1, N_PX, -1))
+
+    t_glue = statistics.median(timed(m_glue, reps, 3))
+    t_fused = statistics.median(timed(m_fused, reps, 3))
+    match_pipeline = {"what": "matching.match (prep + iter_proj + occlusion test + .half() + refine_matches + pixel_to_lin), "
+                              "fp32 descriptors in, identity init, 512x384",
+                      "torch_glue_ms": t_glue, "fused_ms": t_fused, "torch_glue_px_per_s": N_PX / (t_glue * 1e-3),
+                      "fused_px_per_s": N_PX / (t_fused * 1e-3), "fused_launches": 5}
+
     # ---- global optimisation, edge-sharded -------------------------------------------------------
     gopt = None
     if args.global_opt != "none":
@@ -361,7 +377,8 @@ def run_gpu(args):
                            "l2": "L2 flushed (512 MB fill) before every timed step and kernel rep",
                            "parallelism": f"replicas x{world}" if world > 1 else "1 GPU"},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * K,
-                "roofline": roofline, "kernels": kern, "cpu_baseline": cpu, "global_opt": gopt}
+                "roofline": roofline, "kernels": kern, "cpu_baseline": cpu, "global_opt": gopt,
+                "match_pipeline": match_pipeline}
         emit(line)
     if world > 1:
         dist.destroy_process_group()

@@ -79,6 +79,19 @@ int m3r_refine_matches_f64(const double* D11, const double* D21, const int64_t* 
                            int64_t* p1_new, int b, int h, int w, int n, int fdim, int radius,
                            int dilation_max, void* stream);
 
+/* Fused matching.match() (additive; the five reference ops above are unchanged): matching.py:25-90 in
+ * five launches -- ray normalisation + Scharr gradients + p_init (one kernel), LM projection with the
+ * occlusion test |X11[p] - X21| < dist_thresh fused into its epilogue, fp32->fp16 of both descriptor
+ * maps (skipped when they are fp16 already), refine_matches, pixel_to_lin.
+ *   X11, X21 [b,h,w,3] f32; D11, D21 [b,h,w,fdim] f32 (desc_is_f32 = 1) or f16; idx_init [b,h*w] i64 or NULL
+ *   -> idx_out [b,h*w] i64 (u + w v), valid_out [b,h*w] u8.  workspace: m3r_match_workspace_bytes(), 256-B aligned. */
+size_t m3r_match_workspace_bytes(int b, int h, int w, int fdim, int desc_is_f32);
+int m3r_match_fused(const float* X11, const float* X21, const void* D11, const void* D21, int fdim,
+                    int desc_is_f32, const int64_t* idx_init, int b, int h, int w, int max_iter,
+                    float lambda_init, float cost_thresh, float dist_thresh, int radius, int dilation_max,
+                    int64_t* idx_out, uint8_t* valid_out, void* workspace, size_t workspace_bytes,
+                    void* stream);
+
 /* ---- Gauss-Newton ---------------------------------------------------------------------- */
 
 /* Edge sharding for multi-GPU global optimisation (additive; NULL = single GPU, all edges).

@@ -20,7 +20,7 @@ MAX_KF_ID = 1 << 20
 
 EXPORTS = [
     "m3r_abi_version", "m3r_last_error", "m3r_iter_proj", "m3r_iter_proj_ws", "m3r_iter_proj_workspace_bytes",
-    "m3r_refine_matches_f16",
+    "m3r_refine_matches_f16", "m3r_match_workspace_bytes", "m3r_match_fused",
     "m3r_refine_matches_f32", "m3r_refine_matches_f64", "m3r_gn_workspace_bytes", "m3r_gn_workspace_bytes_sharded",
     "m3r_gauss_newton", "m3r_gn_prepare", "m3r_gn_pack", "m3r_gn_accumulate", "m3r_gn_edge_blocks", "m3r_gn_solve_retract",
     "m3r_gn_export_hs_gs", "m3r_pose_retr", "m3r_comm_unique_id", "m3r_comm_init", "m3r_comm_destroy",
@@ -48,6 +48,8 @@ def _load():
     lib.m3r_last_error.restype = C.c_char_p
     lib.m3r_iter_proj_workspace_bytes.restype = C.c_size_t
     lib.m3r_iter_proj_workspace_bytes.argtypes = [C.c_int, C.c_int, C.c_int]
+    lib.m3r_match_workspace_bytes.restype = C.c_size_t
+    lib.m3r_match_workspace_bytes.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
     lib.m3r_gn_workspace_bytes.restype = C.c_size_t
     lib.m3r_gn_workspace_bytes.argtypes = [C.c_int, C.c_int, C.c_int]
     lib.m3r_gn_workspace_bytes_sharded.restype = C.c_size_t
@@ -105,6 +107,33 @@ def iter_proj(rays_img_with_grad, pts_3d_norm, p_init, max_iter, lambda_init, co
                                  _ptr(conv), b, h, w, n, int(max_iter), C.c_float(lambda_init),
                                  C.c_float(cost_thresh), _stream()), "m3r_iter_proj")
     return [p_new, conv]
+
+
+def match_fused(X11, X21, D11, D21, idx_init, max_iter, lambda_init, cost_thresh, dist_thresh, radius,
+                dilation_max):
+    """matching.match() in five launches (m3r_match_fused) -> (idx_1_to_2 int64 [b,n], valid bool [b,n,1])"""
+    _req(X11, "X11", torch.float32)
+    _req(X21, "X21", torch.float32)
+    b, h, w, _ = X11.shape
+    n = h * w
+    D21 = D21.reshape(b, n, -1)
+    fdim = D11.shape[-1]
+    assert D11.dtype == D21.dtype and D11.dtype in (torch.float32, torch.float16)
+    _req(D11, "D11")
+    _req(D21, "D21")
+    is_f32 = 1 if D11.dtype == torch.float32 else 0
+    if idx_init is not None:
+        _req(idx_init, "idx_1_to_2_init", torch.int64)
+    idx = torch.empty((b, n), dtype=torch.int64, device=X11.device)
+    valid = torch.empty((b, n, 1), dtype=torch.bool, device=X11.device)
+    nbytes = int(lib.m3r_match_workspace_bytes(b, h, w, fdim, is_f32))
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=X11.device)
+    _check(lib.m3r_match_fused(_ptr(X11), _ptr(X21), _ptr(D11), _ptr(D21), fdim, is_f32,
+                               _ptr(idx_init) if idx_init is not None else None, b, h, w, int(max_iter),
+                               C.c_float(lambda_init), C.c_float(cost_thresh), C.c_float(dist_thresh), int(radius),
+                               int(dilation_max), _ptr(idx), _ptr(valid), _ptr(ws), C.c_size_t(nbytes), _stream()),
+           "m3r_match_fused")
+    return idx, valid
 
 
 def refine_matches(D11, D21, p1, radius, dilation_max):

@@ -288,12 +288,63 @@ void clear_edge_shard() { g_dist.sharded = false; }
 void set_sync_checks(bool on) { g_dist.sync_checks = on; }
 std::vector<int64_t> last_info() { return g_dist.last_info; }
 
+
+// Additive op (not in the reference module): matching.match() fused into five launches (m3r_match_fused).
+// Returns [idx_1_to_2 i64 [b,n], valid_match2 bool [b,n,1]] like mast3r_slam/matching.py:8-10.
+std::vector<torch::Tensor> match_fused(torch::Tensor X11, torch::Tensor X21, torch::Tensor D11, torch::Tensor D21,
+                                       c10::optional<torch::Tensor> idx_1_to_2_init, const int max_iter,
+                                       const float lambda_init, const float convergence_thresh,
+                                       const float dist_thresh, const int radius, const int dilation_max) {
+  CHECK_CONTIGUOUS(X11);
+  CHECK_CONTIGUOUS(X21);
+  CHECK_CONTIGUOUS(D11);
+  CHECK_CONTIGUOUS(D21);
+  CHECK_CUDA(X11);
+  CHECK_CUDA(X21);
+  CHECK_CUDA(D11);
+  CHECK_CUDA(D21);
+  CHECK_DTYPE(X11, torch::kFloat32);
+  CHECK_DTYPE(X21, torch::kFloat32);
+  TORCH_CHECK(X11.dim() == 4 && X11.size(3) == 3 && X21.sizes() == X11.sizes(), "X11 / X21 must be [b,h,w,3]");
+  TORCH_CHECK(D11.scalar_type() == D21.scalar_type() &&
+                  (D11.scalar_type() == torch::kFloat32 || D11.scalar_type() == torch::kFloat16),
+              "D11 / D21 must both be float32 or float16");
+  const int b = (int)X11.size(0), h = (int)X11.size(1), w = (int)X11.size(2);
+  const int fdim = (int)D11.size(-1);
+  TORCH_CHECK(D11.numel() == (int64_t)b * h * w * fdim && D21.numel() == D11.numel(), "descriptor shape mismatch");
+  const int is_f32 = D11.scalar_type() == torch::kFloat32 ? 1 : 0;
+  const int64_t* init = nullptr;
+  if (idx_1_to_2_init.has_value()) {
+    CHECK_CONTIGUOUS((*idx_1_to_2_init));
+    CHECK_CUDA((*idx_1_to_2_init));
+    CHECK_DTYPE((*idx_1_to_2_init), torch::kInt64);
+    TORCH_CHECK(idx_1_to_2_init->numel() == (int64_t)b * h * w, "idx_1_to_2_init must be [b,h*w]");
+    init = idx_1_to_2_init->data_ptr<int64_t>();
+  }
+  const c10::cuda::CUDAGuard guard(X11.device());
+  auto opts = X11.options();
+  torch::Tensor idx = torch::empty({b, (int64_t)h * w}, opts.dtype(torch::kInt64));
+  torch::Tensor valid = torch::empty({b, (int64_t)h * w, 1}, opts.dtype(torch::kBool));
+  const size_t ws_bytes = m3r_match_workspace_bytes(b, h, w, fdim, is_f32);
+  torch::Tensor ws = torch::empty({(int64_t)std::max<size_t>(ws_bytes, 256)}, opts.dtype(torch::kUInt8));
+  int rc = m3r_match_fused(X11.data_ptr<float>(), X21.data_ptr<float>(), D11.data_ptr(), D21.data_ptr(), fdim, is_f32,
+                           init, b, h, w, max_iter, lambda_init, convergence_thresh, dist_thresh, radius, dilation_max,
+                           idx.data_ptr<int64_t>(), reinterpret_cast<uint8_t*>(valid.data_ptr<bool>()), ws.data_ptr(),
+                           ws_bytes, cur_stream());
+  check_rc(rc, "m3r_match_fused");
+  return {idx, valid};
+}
+
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("gauss_newton_points", &gauss_newton_points, "gauss newton points");
   m.def("gauss_newton_rays", &gauss_newton_rays, "gauss newton rays");
   m.def("gauss_newton_calib", &gauss_newton_calib, "gauss newton calib");
   m.def("iter_proj", &iter_proj, "iterative projection matching");
   m.def("refine_matches", &refine_matches, "refine matches");
+  m.def("match_fused", &match_fused, "fused matching.match (additive)", py::arg("X11"), py::arg("X21"), py::arg("D11"),
+        py::arg("D21"), py::arg("idx_1_to_2_init") = py::none(), py::arg("max_iter") = 10,
+        py::arg("lambda_init") = 1e-8f, py::arg("convergence_thresh") = 1e-6f, py::arg("dist_thresh") = 1e-1f,
+        py::arg("radius") = 3, py::arg("dilation_max") = 5);
   m.def("nccl_unique_id", &nccl_unique_id);
   m.def("init_distributed", &init_distributed);
   m.def("shutdown_distributed", &shutdown_distributed);

@@ -17,6 +17,8 @@
 //                       only the 6 gradient channels are gathered at the new pixel.
 // After convergence almost every step is a reject, so an iteration costs 12 gathers instead of 48.
 // One thread per target direction, 128-thread CTAs (4 warps), grid sized over all of b*n.
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 
 namespace m3r {
@@ -271,11 +273,21 @@ __device__ __forceinline__ Normal normal_eq_p(const TapsP& t, const float err[3]
   return s;
 }
 
+// POST = true (fused matching glue, matching.py:68-76): instead of the float pixel the kernel writes the
+// truncated int64 pixel p1 = (long)(u, v) and valid = converged && |X11[p1] - X21[k]| < dist_thresh.
+struct IterProjPost {
+  const float* X11;   // [b,h,w,3]
+  const float* X21;   // [b,n,3]
+  int64_t* p1;        // [b,n,2]
+  float dist_thresh;
+};
+
+template <bool POST>
 __global__ void __launch_bounds__(kIterProjThreads)
 iter_proj_padded_kernel(const float4* __restrict__ rays_pad, const float* __restrict__ pts3d_norm,
                         const float* __restrict__ p_init, float* __restrict__ p_new,
                         uint8_t* __restrict__ converged, int h, int w, int n, int max_iter,
-                        float lambda_init, float cost_thresh) {
+                        float lambda_init, float cost_thresh, IterProjPost post) {
   const int k = blockIdx.x * kIterProjThreads + threadIdx.x;
   const int b = blockIdx.y;
   if (k >= n) return;
@@ -322,8 +334,115 @@ iter_proj_padded_kernel(const float4* __restrict__ rays_pad, const float* __rest
       }
     }
   }
-  reinterpret_cast<float2*>(p_new)[pix] = make_float2(u, v);
-  converged[pix] = conv ? 1 : 0;
+  if (POST) {
+    const int pu = static_cast<int>(u), pv = static_cast<int>(v);  // .long(): truncation (u, v >= 1)
+    const float* a = post.X11 + (static_cast<size_t>(b) * h * w + static_cast<size_t>(pv) * w + pu) * 3;
+    const float* q = post.X21 + pix * 3;
+    const float d0 = __ldg(a + 0) - __ldg(q + 0), d1 = __ldg(a + 1) - __ldg(q + 1), d2 = __ldg(a + 2) - __ldg(q + 2);
+    const float dist = sqrtf(d0 * d0 + d1 * d1 + d2 * d2);
+    reinterpret_cast<longlong2*>(post.p1)[pix] = make_longlong2(pu, pv);
+    converged[pix] = (conv && dist < post.dist_thresh) ? 1 : 0;
+  } else {
+    reinterpret_cast<float2*>(p_new)[pix] = make_float2(u, v);
+    converged[pix] = conv ? 1 : 0;
+  }
+}
+
+// ---- fused matching glue: prep (matching.py:25-49 + image.py:5-38) -------------------------------------
+// One kernel replaces F.normalize, permute, reflect pad, two grouped 3x3 convolutions, cat, permute +
+// contiguous, the second F.normalize and the arange / lin_to_pixel / float chain (~12 torch kernels that
+// move 4-5x the bytes of iter_proj itself).  A CTA normalises a (32+2) x (8+2) patch of X11 into shared
+// memory (reflect padding at the image border), applies the Scharr-like gradients
+// 1/32 [[-3,0,3],[-10,0,10],[-3,0,3]] and its transpose, and writes the 48-byte texels the LM kernel reads;
+// the same thread normalises X21[k] and emits p_init[k] for its own pixel index k.
+constexpr int kPrepTW = 32, kPrepTH = 8;
+
+__device__ __forceinline__ int reflect(int i, int n) { return i < 0 ? -i : (i >= n ? 2 * n - 2 - i : i); }
+
+__global__ void __launch_bounds__(kPrepTW * kPrepTH)
+match_prep_kernel(const float* __restrict__ X11, const float* __restrict__ X21, const int64_t* __restrict__ idx_init,
+                  float4* __restrict__ rays_pad, float* __restrict__ pts3d_norm, float* __restrict__ p_init, int h,
+                  int w) {
+  __shared__ float s_r[3][kPrepTH + 2][kPrepTW + 2 + 1];
+  const int b = blockIdx.z;
+  const int x0 = blockIdx.x * kPrepTW, y0 = blockIdx.y * kPrepTH;
+  const int tid = threadIdx.y * kPrepTW + threadIdx.x;
+  const float* img = X11 + static_cast<size_t>(b) * h * w * 3;
+  for (int t = tid; t < (kPrepTH + 2) * (kPrepTW + 2); t += kPrepTW * kPrepTH) {
+    const int ly = t / (kPrepTW + 2), lx = t % (kPrepTW + 2);
+    const int gy = reflect(min(y0 + ly - 1, h), h), gx = reflect(min(x0 + lx - 1, w), w);  // clamp keeps reflect in range
+    const float* p = img + (static_cast<size_t>(gy) * w + gx) * 3;
+    const float a0 = __ldg(p), a1 = __ldg(p + 1), a2 = __ldg(p + 2);
+    const float nrm = fmaxf(sqrtf(a0 * a0 + a1 * a1 + a2 * a2), 1e-12f);  // F.normalize: x / max(|x|, eps)
+    s_r[0][ly][lx] = a0 / nrm;
+    s_r[1][ly][lx] = a1 / nrm;
+    s_r[2][ly][lx] = a2 / nrm;
+  }
+  __syncthreads();
+  const int x = x0 + threadIdx.x, y = y0 + threadIdx.y;
+  if (x >= w || y >= h) return;
+  const int lx = threadIdx.x + 1, ly = threadIdx.y + 1;
+  float r[3], gx[3], gy[3];
+  const float k3 = 3.0f / 32.0f, k10 = 10.0f / 32.0f;
+#pragma unroll
+  for (int c = 0; c < 3; c++) {
+    const float (*s)[kPrepTW + 2 + 1] = s_r[c];
+    r[c] = s[ly][lx];
+    gx[c] = k3 * (s[ly - 1][lx + 1] - s[ly - 1][lx - 1]) + k10 * (s[ly][lx + 1] - s[ly][lx - 1]) +
+            k3 * (s[ly + 1][lx + 1] - s[ly + 1][lx - 1]);
+    gy[c] = k3 * (s[ly + 1][lx - 1] - s[ly - 1][lx - 1]) + k10 * (s[ly + 1][lx] - s[ly - 1][lx]) +
+            k3 * (s[ly + 1][lx + 1] - s[ly - 1][lx + 1]);
+  }
+  const size_t k = static_cast<size_t>(y) * w + x;
+  const size_t pix = static_cast<size_t>(b) * h * w + k;
+  rays_pad[pix * kPadF4 + 0] = make_float4(r[0], r[1], r[2], gx[0]);
+  rays_pad[pix * kPadF4 + 1] = make_float4(gx[1], gx[2], gy[0], gy[1]);
+  rays_pad[pix * kPadF4 + 2] = make_float4(gy[2], 0.f, 0.f, 0.f);
+  {
+    const float* q = X21 + pix * 3;
+    const float a0 = __ldg(q), a1 = __ldg(q + 1), a2 = __ldg(q + 2);
+    const float nrm = fmaxf(sqrtf(a0 * a0 + a1 * a1 + a2 * a2), 1e-12f);
+    pts3d_norm[pix * 3 + 0] = a0 / nrm;
+    pts3d_norm[pix * 3 + 1] = a1 / nrm;
+    pts3d_norm[pix * 3 + 2] = a2 / nrm;
+  }
+  {
+    const int64_t lin = idx_init ? idx_init[pix] : static_cast<int64_t>(k);
+    reinterpret_cast<float2*>(p_init)[pix] = make_float2(static_cast<float>(lin % w), static_cast<float>(lin / w));
+  }
+}
+
+// p1 [b,n,2] int64 (u, v) -> u + w * v  (matching.py:13-15), elementwise
+__global__ void pixel_to_lin_kernel(const int64_t* __restrict__ p1, int64_t* __restrict__ lin, size_t count, int w) {
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= count) return;
+  const longlong2 p = __ldg(reinterpret_cast<const longlong2*>(p1) + i);
+  lin[i] = p.x + static_cast<int64_t>(w) * p.y;
+}
+
+// descriptors to fp16 (matching.py:80-81 `.half()`), both tensors in one launch; counts are multiples of 8
+__global__ void f32_to_f16_pair_kernel(const float4* __restrict__ a, uint4* __restrict__ ah, size_t na8,
+                                       const float4* __restrict__ c, uint4* __restrict__ ch, size_t nc8) {
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const float4* src;
+  uint4* dst;
+  size_t j;
+  if (i < na8) {
+    src = a; dst = ah; j = i;
+  } else if (i < na8 + nc8) {
+    src = c; dst = ch; j = i - na8;
+  } else {
+    return;
+  }
+  const float4 lo = __ldg(src + 2 * j), hi = __ldg(src + 2 * j + 1);
+  const __half2 h0 = __floats2half2_rn(lo.x, lo.y), h1 = __floats2half2_rn(lo.z, lo.w);
+  const __half2 h2 = __floats2half2_rn(hi.x, hi.y), h3 = __floats2half2_rn(hi.z, hi.w);
+  uint4 o;
+  o.x = *reinterpret_cast<const uint32_t*>(&h0);
+  o.y = *reinterpret_cast<const uint32_t*>(&h1);
+  o.z = *reinterpret_cast<const uint32_t*>(&h2);
+  o.w = *reinterpret_cast<const uint32_t*>(&h3);
+  dst[j] = o;
 }
 
 }  // namespace
@@ -370,8 +489,98 @@ extern "C" int m3r_iter_proj_ws(const float* rays_img, const float* pts3d_norm, 
       rays_img, pad, npix);
   M3R_LAUNCH_CHECK();
   dim3 grid((n + m3r::kIterProjThreads - 1) / m3r::kIterProjThreads, b);
-  m3r::iter_proj_padded_kernel<<<grid, m3r::kIterProjThreads, 0, st>>>(pad, pts3d_norm, p_init, p_new, converged, h,
-                                                                      w, n, max_iter, lambda_init, cost_thresh);
+  m3r::iter_proj_padded_kernel<false><<<grid, m3r::kIterProjThreads, 0, st>>>(
+      pad, pts3d_norm, p_init, p_new, converged, h, w, n, max_iter, lambda_init, cost_thresh, m3r::IterProjPost{});
+  M3R_LAUNCH_CHECK();
+  return M3R_OK;
+}
+
+// ---- fused matching: matching.match() in five launches ------------------------------------------------
+namespace {
+struct MatchWs {
+  size_t off_rays, off_pts, off_p0, off_p1, off_p1r, off_d11h, off_d21h, total;
+};
+MatchWs match_ws_layout(int b, int h, int w, int fdim, int desc_is_f32) {
+  MatchWs L{};
+  const size_t n = static_cast<size_t>(b) * h * w;
+  size_t o = 0;
+  auto take = [&](size_t bytes) {
+    const size_t r = o;
+    o = m3r::align_up(o + bytes, 256);
+    return r;
+  };
+  L.off_rays = take(n * m3r::kPadF4 * sizeof(float4));
+  L.off_pts = take(n * 3 * sizeof(float));
+  L.off_p0 = take(n * 2 * sizeof(float));
+  L.off_p1 = take(n * 2 * sizeof(int64_t));
+  L.off_p1r = take(n * 2 * sizeof(int64_t));
+  L.off_d11h = take(desc_is_f32 ? n * fdim * 2 : 0);
+  L.off_d21h = take(desc_is_f32 ? n * fdim * 2 : 0);
+  L.total = o;
+  return L;
+}
+}  // namespace
+
+extern "C" size_t m3r_match_workspace_bytes(int b, int h, int w, int fdim, int desc_is_f32) {
+  if (b < 1 || h < 1 || w < 1 || fdim < 1) return 0;
+  return match_ws_layout(b, h, w, fdim, desc_is_f32).total;
+}
+
+extern "C" int m3r_match_fused(const float* X11, const float* X21, const void* D11, const void* D21, int fdim,
+                               int desc_is_f32, const int64_t* idx_init, int b, int h, int w, int max_iter,
+                               float lambda_init, float cost_thresh, float dist_thresh, int radius,
+                               int dilation_max, int64_t* idx_out, uint8_t* valid_out, void* workspace,
+                               size_t workspace_bytes, void* stream) {
+  if (!X11 || !X21 || !idx_out || !valid_out || !workspace) return M3R_ERR_BAD_ARG;
+  if (radius > 0 && (!D11 || !D21)) return M3R_ERR_BAD_ARG;
+  if (b < 0 || h < 3 || w < 3 || fdim < 1 || max_iter < 0 || radius < 0 || dilation_max < 0) return M3R_ERR_BAD_ARG;
+  if (b == 0) return M3R_OK;
+  if (b > 65535) return M3R_ERR_BAD_ARG;
+  const size_t n_all = static_cast<size_t>(b) * h * w;
+  if (static_cast<size_t>(h) * w > 0x7fffffffull) return M3R_ERR_UNSUPPORTED;
+  if (radius > 0 && desc_is_f32 && (n_all * fdim) % 8 != 0) return M3R_ERR_UNSUPPORTED;
+  if ((reinterpret_cast<uintptr_t>(workspace) & 255) != 0) return M3R_ERR_WORKSPACE;
+  const MatchWs L = match_ws_layout(b, h, w, fdim, desc_is_f32);
+  if (workspace_bytes < L.total) return M3R_ERR_WORKSPACE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  char* ws = static_cast<char*>(workspace);
+  float4* rays = reinterpret_cast<float4*>(ws + L.off_rays);
+  float* pts = reinterpret_cast<float*>(ws + L.off_pts);
+  float* p0 = reinterpret_cast<float*>(ws + L.off_p0);
+  int64_t* p1 = reinterpret_cast<int64_t*>(ws + L.off_p1);
+  int64_t* p1r = reinterpret_cast<int64_t*>(ws + L.off_p1r);
+  const int n = h * w;
+  {
+    dim3 grid((w + m3r::kPrepTW - 1) / m3r::kPrepTW, (h + m3r::kPrepTH - 1) / m3r::kPrepTH, b);
+    m3r::match_prep_kernel<<<grid, dim3(m3r::kPrepTW, m3r::kPrepTH), 0, st>>>(X11, X21, idx_init, rays, pts, p0, h, w);
+    M3R_LAUNCH_CHECK();
+  }
+  {
+    m3r::IterProjPost post{X11, X21, p1, dist_thresh};
+    dim3 grid((n + m3r::kIterProjThreads - 1) / m3r::kIterProjThreads, b);
+    m3r::iter_proj_padded_kernel<true><<<grid, m3r::kIterProjThreads, 0, st>>>(
+        rays, pts, p0, nullptr, valid_out, h, w, n, max_iter, lambda_init, cost_thresh, post);
+    M3R_LAUNCH_CHECK();
+  }
+  const int64_t* p_final = p1;
+  if (radius > 0) {
+    const void* d11h = D11;
+    const void* d21h = D21;
+    if (desc_is_f32) {
+      const size_t n8 = n_all * fdim / 8;
+      uint4* a = reinterpret_cast<uint4*>(ws + L.off_d11h);
+      uint4* c = reinterpret_cast<uint4*>(ws + L.off_d21h);
+      m3r::f32_to_f16_pair_kernel<<<static_cast<unsigned>((2 * n8 + 255) / 256), 256, 0, st>>>(
+          static_cast<const float4*>(D11), a, n8, static_cast<const float4*>(D21), c, n8);
+      M3R_LAUNCH_CHECK();
+      d11h = a;
+      d21h = c;
+    }
+    const int rc = m3r_refine_matches_f16(d11h, d21h, p1, p1r, b, h, w, n, fdim, radius, dilation_max, stream);
+    if (rc != M3R_OK) return rc;
+    p_final = p1r;
+  }
+  m3r::pixel_to_lin_kernel<<<static_cast<unsigned>((n_all + 255) / 256), 256, 0, st>>>(p_final, idx_out, n_all, w);
   M3R_LAUNCH_CHECK();
   return M3R_OK;
 }

@@ -1,8 +1,8 @@
 """Mirror of the reference's matching glue (mast3r_slam/matching.py:8-90, image.py:5-38) on top of
 the B200 ops.  Same function names, arguments and return values; the config dict is passed in
 instead of read from the reference's global (defaults = config/base.yaml:15-21).  The torch glue
-(normalise, Scharr-like gradients, occlusion test) is unchanged reference behaviour — SURVEY §8f-1
-lists fusing it as the next row, it is not part of the five ops.
+(normalise, Scharr-like gradients, occlusion test) is unchanged reference behaviour; `match(...,
+fused=True)` is the additive fused path of SURVEY §8f-1 (csrc/iter_proj.cu: m3r_match_fused).
 """
 import torch
 import torch.nn.functional as F
@@ -63,6 +63,15 @@ def match_iterative_proj(X11, X21, D11, D21, idx_1_to_2_init=None, cfg=None, ops
     return pixel_to_lin(p1, w), valid_proj2.unsqueeze(-1)
 
 
-def match(X11, X21, D11, D21, idx_1_to_2_init=None, cfg=None, ops=None):
-    """matching.py:8-10"""
+def match(X11, X21, D11, D21, idx_1_to_2_init=None, cfg=None, ops=None, fused=False):
+    """matching.py:8-10.  fused=True (additive): the whole function runs as five launches of
+    m3r_match_fused instead of ~20 torch kernels around the two ops; same outputs within the parity bar
+    (the torch glue's normalise / conv arithmetic is not reproduced bit for bit)."""
+    if fused:
+        from . import abi
+        cfg = dict(DEFAULT_CFG, **(cfg or {}))
+        b, h, w = X21.shape[:3]
+        return abi.match_fused(X11.contiguous(), X21.contiguous(), D11.contiguous(), D21.reshape(b, h * w, -1).contiguous(),
+                               idx_1_to_2_init, cfg["max_iter"], cfg["lambda_init"], cfg["convergence_thresh"],
+                               cfg["dist_thresh"], cfg["radius"], cfg["dilation_max"])
     return match_iterative_proj(X11, X21, D11, D21, idx_1_to_2_init, cfg, ops)

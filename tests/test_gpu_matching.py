@@ -224,6 +224,26 @@ def test_match_pipeline_vs_reference_cuda(backends, ref_backends, synth):
         assert err.median() <= 1.5
 
 
+@pytest.mark.parametrize("h,w,b,half", [(96, 128, 2, False), (384, 512, 1, False), (50, 70, 1, True)])
+def test_match_fused_vs_torch_glue(backends, synth, h, w, b, half):
+    """m3r_match_fused (prep + LM with fused occlusion test + fp16 conversion + refine + pixel_to_lin) against
+    matching.match with the torch glue around the same two ops: BASELINE bar (>= 99.9 % identical, <= 1 px),
+    identity and previous-frame initialisation, partial tiles, fp32 and fp16 descriptors, radius 0"""
+    need_gpu()
+    m = pkg("matching")
+    d = synth.make_matching_pair(h, w, b=b, seed=11 + h, device="cuda")
+    D11, D21 = (d["D11"].half(), d["D21"].half()) if half else (d["D11"], d["D21"])
+    for init in (None, d["idx_init"]):
+        for cfg in (None, {"radius": 0}):
+            idx_a, val_a = m.match(d["X11"], d["X21"], D11, D21, init, cfg=cfg, fused=True)
+            idx_b, val_b = m.match(d["X11"], d["X21"], D11, D21, init, cfg=cfg, ops=backends)
+            assert idx_a.shape == idx_b.shape and val_a.shape == val_b.shape and val_a.dtype == torch.bool
+            same, worst = match_agreement(np_(m.lin_to_pixel(idx_a, w)), np_(m.lin_to_pixel(idx_b, w)))
+            agree_valid = (val_a == val_b).float().mean().item()
+            assert same >= 0.999 and worst <= 1, (same, worst, init is None, cfg)
+            assert agree_valid >= 0.999, agree_valid
+
+
 def test_drop_in_module_equals_c_abi(backends, synth):
     need_gpu()
     mod = pkg().load_drop_in()
@@ -234,3 +254,6 @@ def test_drop_in_module_equals_c_abi(backends, synth):
     p1 = a[0].long()
     D11, D21 = d["D11"].half(), d["D21"].view(1, 96 * 128, -1).half()
     assert torch.equal(backends.refine_matches(D11, D21, p1, 3, 5)[0], mod.refine_matches(D11, D21, p1, 3, 5)[0])
+    fa = pkg("matching").match(d["X11"], d["X21"], d["D11"], d["D21"], None, fused=True)
+    fb = mod.match_fused(d["X11"], d["X21"], d["D11"], d["D21"].view(1, 96 * 128, -1))
+    assert torch.equal(fa[0], fb[0]) and torch.equal(fa[1], fb[1])
