@@ -159,7 +159,7 @@ constexpr int kTile = 16;                     // 16 x 16 queries per CTA
 constexpr int kStThreads = kTile * kTile;     // 256
 constexpr int kStRadius = 3, kStCnt = 7;
 constexpr int kStMaxLevels = 8;
-constexpr int kCapPx = 2304;                  // staged pixels per pass: 110 592 B -> 2 CTAs / SM
+constexpr int kCapPx = 2304;                  // staged pixels per pass: 110 592 B -> 2 CTAs / SM (3 CTAs x 72 KB measured slower: 177 vs 166 us)
 constexpr int kStSmemBytes = kCapPx * kPxBytes;
 constexpr int kSane = 1 << 16;                // |centre| beyond this never enters the box statistics
 constexpr int kInlierRad = 12;                // robust pass: centres within +-12 px of the tile mean
@@ -358,6 +358,10 @@ refine_staged_kernel(const __half* __restrict__ D11, const __half* __restrict__ 
       }
     }
     const int bh = py1 - py0 + 1;
+    if (have_box && bh > 0 && (umax - umin + 1) * bh > kCapPx) {  // (large dilations: even the robust box is too big)
+      have_box = false;
+      inl = false;
+    }
     // ---- passes over groups of u-offset columns -------------------------------------------------
     if (have_box && bh > 0) {
       // Row pitch = width rounded up to 8 px (384 B): a 16-byte chunk of pixel (x, y) then lands in bank
