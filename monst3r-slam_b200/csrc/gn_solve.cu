@@ -208,7 +208,7 @@ __device__ __forceinline__ void grid_barrier() {
 // tile in registers (lane r owns row r of A / L, then lane c owns column c of L^-1): no block
 // barriers inside, pivots broadcast by shuffle.  Ls <- L (upper part zeroed), Li <- L^-1.
 // Returns (to every thread, through s_flag) false on a pivot <= 0.
-__device__ bool tile_potrf_invert(double (*Ls)[kTile + 1], double (*Li)[kTile + 1], double* s_dinv, int* s_flag) {
+__device__ __forceinline__ bool tile_potrf_invert(double (*Ls)[kTile + 1], double (*Li)[kTile + 1], double* s_dinv, int* s_flag) {
   const int lane = threadIdx.x;
   if (threadIdx.x < 32) {
     double a[kTile];
@@ -255,6 +255,9 @@ __device__ bool tile_potrf_invert(double (*Ls)[kTile + 1], double (*Li)[kTile + 
   return *s_flag == 0;
 }
 
+// measured (tools/solve_prof.py): dim 1785 (56 tiles) 1.90 -> 1.66 ms with the look-ahead, dim 217 (7 tiles) 139 -> 160 us
+constexpr int kLookaheadMinTiles = 12;
+
 template <bool COOP>
 __global__ void __launch_bounds__(kSolveThreads, 2)
 gn_solve_kernel(const SolveArgs a) {
@@ -271,6 +274,7 @@ gn_solve_kernel(const SolveArgs a) {
   double* H = a.hd;
   const int nfree = a.N - 1;
 
+  if (blockIdx.x == 0 && tid == 0) a.ctrl[CTRL_FAIL_NOW] = 0;  // set by the look-ahead factorisation (phase B)
   // ---------------------------------------------------------------- A. assemble
   // strips: 0..nfree-1 pose strips (7 rows), then padding rows [dim, dimP), then the rhs tile row
   const int nstrips = nfree + 2;
@@ -329,33 +333,84 @@ gn_solve_kernel(const SolveArgs a) {
 #endif
   // ---------------------------------------------------------------- B. Cholesky
   bool failed = false;
+  // Look-ahead: from step 1 on the diagonal tile is factored and inverted DURING the previous step's trailing
+  // update by one dedicated CTA (the last one), which updates tile (kb+1, kb+1) first and takes no other tile,
+  // so the ~8 us serial potrf + inverse leaves the critical path whenever the update has more than a few tiles
+  // per CTA.  The other CTAs then only read L_kk^-1 (8 KB) at the start of the step.
+  const bool lookahead = COOP && gridDim.x > 1 && nblk >= kLookaheadMinTiles;
+  const int diag_cta = (int)gridDim.x - 1;
+  const bool is_diag = lookahead && (int)blockIdx.x == diag_cta;
+  const int n_work = lookahead ? (int)gridDim.x - 1 : (int)gridDim.x;  // CTAs that share the bulk work
   for (int kb = 0; kb < nblk; kb++) {
-    // B1: diagonal tile (redundant per CTA), inverse, TRSM on this CTA's panel tiles
-    for (int t = tid; t < kTile * kTile; t += kSolveThreads) {
-      const int r = t >> 5, c = t & 31;
-      sA[r][c] = (c <= r) ? __ldcg(&H[(size_t)(kb * kTile + r) * ld + kb * kTile + c]) : 0.0;
-    }
-    __syncthreads();
-    if (!tile_potrf_invert(sA, sB, s_dinv, &s_flag)) failed = true;  // sA = L_kk, sB = L_kk^-1
-    SLV(0);
-    if (blockIdx.x == 0) {
+    // B1: diagonal tile, inverse, TRSM on this CTA's panel tiles
+    if (kb == 0 || !lookahead) {
       for (int t = tid; t < kTile * kTile; t += kSolveThreads) {
         const int r = t >> 5, c = t & 31;
-        a.linv[(size_t)kb * kTile * kTile + t] = sB[r][c];
-        if (c <= r) H[(size_t)(kb * kTile + r) * ld + kb * kTile + c] = sA[r][c];
+        sA[r][c] = (c <= r) ? __ldcg(&H[(size_t)(kb * kTile + r) * ld + kb * kTile + c]) : 0.0;
       }
-    }
-    for (int I = kb + 1 + blockIdx.x; I <= nblk; I += gridDim.x) {
-      // X = A_Ik * L_kk^-T :  X[r][c] = sum_{m <= c} A[r][m] * Linv[c][m]
+      __syncthreads();
+      if (!tile_potrf_invert(sA, sB, s_dinv, &s_flag)) failed = true;  // sA = L_kk, sB = L_kk^-1 (redundant per CTA)
+      if (blockIdx.x == 0) {
+        for (int t = tid; t < kTile * kTile; t += kSolveThreads) {
+          const int r = t >> 5, c = t & 31;
+          a.linv[(size_t)kb * kTile * kTile + t] = sB[r][c];
+          if (c <= r) H[(size_t)(kb * kTile + r) * ld + kb * kTile + c] = sA[r][c];
+        }
+      }
+    } else if (!is_diag) {
       __syncthreads();
       for (int t = tid; t < kTile * kTile; t += kSolveThreads)
-        sA[t >> 5][t & 31] = __ldcg(&H[(size_t)(I * kTile + (t >> 5)) * ld + kb * kTile + (t & 31)]);
+        sB[t >> 5][t & 31] = __ldcg(&a.linv[(size_t)kb * kTile * kTile + t]);
+      if (__ldcg(&a.ctrl[CTRL_FAIL_NOW])) failed = true;
       __syncthreads();
-      for (int t = tid; t < kTile * kTile; t += kSolveThreads) {
-        const int r = t >> 5, c = t & 31;
-        double s = 0.0;
-        for (int m = 0; m <= c; m++) s += sA[r][m] * sB[c][m];
-        H[(size_t)(I * kTile + r) * ld + kb * kTile + c] = s;
+    }  // (the diagonal CTA still holds L_kk^-1 in sB from its own factorisation)
+    SLV(0);
+    if (is_diag) {
+      // The serial chain of the factorisation lives in this CTA alone: panel tile (kb+1, kb) -> X = A L_kk^-T
+      // here; after the barrier, while the others update the trailing matrix, diagonal tile (kb+1, kb+1) -= X X^T
+      // is factored + inverted and L_(kb+1)^-1 published for the next step.
+      const int kn = kb + 1;
+      if (kn < nblk) {
+        __syncthreads();
+        for (int t = tid; t < kTile * kTile; t += kSolveThreads)
+          sA[t >> 5][t & 31] = __ldcg(&H[(size_t)(kn * kTile + (t >> 5)) * ld + kb * kTile + (t & 31)]);
+        __syncthreads();
+        double x[kTile * kTile / kSolveThreads];
+#pragma unroll
+        for (int q = 0; q < kTile * kTile / kSolveThreads; q++) {
+          const int t = tid + q * kSolveThreads, r = t >> 5, c = t & 31;
+          double acc = 0.0;
+          for (int m = 0; m <= c; m++) acc += sA[r][m] * sB[c][m];
+          x[q] = acc;
+          H[(size_t)(kn * kTile + r) * ld + kb * kTile + c] = acc;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int q = 0; q < kTile * kTile / kSolveThreads; q++) {
+          const int t = tid + q * kSolveThreads;
+          sA[t >> 5][t & 31] = x[q];
+        }
+        __syncthreads();
+      }
+    } else {
+      // panel tiles of this CTA (with look-ahead, tile (kb+1, kb) belongs to the diagonal CTA unless it is the rhs row)
+      for (int I = kb + 1 + ((lookahead && kb + 1 < nblk) ? 1 : 0) + blockIdx.x; I <= nblk; I += n_work) {
+        // X = A_Ik * L_kk^-T :  X[r][c] = sum_{m <= c} A[r][m] * Linv[c][m]
+        __syncthreads();
+        for (int t = tid; t < kTile * kTile; t += kSolveThreads)
+          sA[t >> 5][t & 31] = __ldcg(&H[(size_t)(I * kTile + (t >> 5)) * ld + kb * kTile + (t & 31)]);
+        __syncthreads();
+        {  // 4 outputs per thread, all 32 terms (L^-1 carries an explicit zero upper triangle): unrolled, 4-way ILP
+          const int c = tid & 31, r0 = tid >> 5;
+          double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+#pragma unroll 8
+          for (int m = 0; m < kTile; m++) {
+            const double l = sB[c][m];
+            s0 += sA[r0][m] * l; s1 += sA[r0 + 8][m] * l; s2 += sA[r0 + 16][m] * l; s3 += sA[r0 + 24][m] * l;
+          }
+          double* o = &H[(size_t)(I * kTile) * ld + kb * kTile + c];
+          o[(size_t)r0 * ld] = s0; o[(size_t)(r0 + 8) * ld] = s1; o[(size_t)(r0 + 16) * ld] = s2; o[(size_t)(r0 + 24) * ld] = s3;
+        }
       }
     }
     SLV(1);
@@ -366,7 +421,48 @@ gn_solve_kernel(const SolveArgs a) {
     const int ncols = rem - 1;          // tile columns kb+1 .. nblk-1
     // tiles enumerated row by row: row i (1..rem) has min(i, ncols) tiles
     const int ntiles = ncols * (ncols + 1) / 2 + ncols;  // triangle + rhs row
-    for (int t0 = blockIdx.x; t0 < ntiles; t0 += gridDim.x) {
+    if (is_diag && kb + 1 < nblk) {
+      // while the other CTAs run the trailing update: diagonal tile (kb+1, kb+1) -= X X^T (X is still in sA),
+      // factor + invert it and publish L^-1 for the next step
+      const int kn = kb + 1;
+        {  // D = A_(kn,kn) - X X^T into sB (L_kk^-1 is no longer needed here)
+          const int r = tid >> 4, c = tid & 15;
+          double acc00 = 0, acc01 = 0, acc10 = 0, acc11 = 0;
+#pragma unroll 8
+          for (int m = 0; m < kTile; m++) {
+            const double a0 = sA[r][m], a1 = sA[r + 16][m], b0 = sA[c][m], b1 = sA[c + 16][m];
+            acc00 += a0 * b0; acc01 += a0 * b1; acc10 += a1 * b0; acc11 += a1 * b1;
+          }
+          const double* o = &H[(size_t)(kn * kTile) * ld + kn * kTile];
+          const double d00 = __ldcg(&o[(size_t)r * ld + c]) - acc00;
+          const double d01 = __ldcg(&o[(size_t)r * ld + c + 16]) - acc01;
+          const double d10 = __ldcg(&o[(size_t)(r + 16) * ld + c]) - acc10;
+          const double d11 = __ldcg(&o[(size_t)(r + 16) * ld + c + 16]) - acc11;
+          __syncthreads();
+          sB[r][c] = (c <= r) ? d00 : 0.0;
+          sB[r][c + 16] = (c + 16 <= r) ? d01 : 0.0;
+          sB[r + 16][c] = d10;  // c <= 15 < r + 16
+          sB[r + 16][c + 16] = (c <= r) ? d11 : 0.0;
+        }
+        __syncthreads();
+        const bool ok = tile_potrf_invert(sB, sA, s_dinv, &s_flag);  // sB = L, sA = L^-1
+        for (int t = tid; t < kTile * kTile; t += kSolveThreads) {
+          const int r = t >> 5, c = t & 31;
+          a.linv[(size_t)kn * kTile * kTile + t] = sA[r][c];
+          if (c <= r) H[(size_t)(kn * kTile + r) * ld + kn * kTile + c] = sB[r][c];
+        }
+        if (!ok) {
+          failed = true;
+          if (tid == 0) a.ctrl[CTRL_FAIL_NOW] = 1;
+        }
+        __syncthreads();
+        for (int t = tid; t < kTile * kTile; t += kSolveThreads) sB[t >> 5][t & 31] = sA[t >> 5][t & 31];
+        __syncthreads();
+    }
+    // with look-ahead tile 0 = (kb+1, kb+1) is updated (and factored) by the diagonal CTA
+    const int t_first = lookahead ? (is_diag ? ntiles : 1 + (int)blockIdx.x) : (int)blockIdx.x;
+    const int t_step = n_work;
+    for (int t0 = t_first; t0 < ntiles; t0 += t_step) {
       int i, j;
       if (t0 < ncols * (ncols + 1) / 2) {
         // invert the triangular number: i = row (0-based within triangle), j <= i
@@ -406,29 +502,98 @@ gn_solve_kernel(const SolveArgs a) {
     grid_barrier<COOP>();
     SLV(4);
   }
-  if (blockIdx.x != 0) return;
-
-  // ---------------------------------------------------------------- C. back-substitution (CTA 0)
-  for (int t = tid; t < dimP; t += kSolveThreads) s_x[t] = __ldcg(&H[(size_t)dimP * ld + t]);  // y = L^-1 g
-  __syncthreads();
-  for (int kb = nblk - 1; kb >= 0; kb--) {
-    // x_kb = L_kk^-T s_kb : x[c] = sum_{m >= c} Linv[m][c] * s[m]
+  // ---------------------------------------------------------------- C. back-substitution  L^T x = y
+  const bool par_back = COOP && nblk >= 2 && nblk <= (int)gridDim.x;
+  if (par_back) {
+    // Column-block dataflow, no grid barriers: CTA kb owns x_kb = L_kk^-T (y_kb - sum_{j>kb} L_jk^T x_j).  The x_j
+    // travel through global memory as {flag:32 | half of the double:32} words (8-byte stores are single-copy
+    // atomic, so a word with the flag also has its payload): a CTA polls x_j while the tile L_jk it needs next is
+    // already in its registers.  Chain = one publish + one 32x32 GEMV per block instead of CTA 0 streaming the
+    // whole factor through one SM.  The words live in rows dimP+2.. of the rhs tile row, which hold zeros after
+    // the factorisation (zero rows stay zero under TRSM / updates).  CTA 0 ends up with all of x in s_x.
+    const int kb = blockIdx.x;
+    if (kb >= nblk) return;
+    unsigned long long* xw = reinterpret_cast<unsigned long long*>(&H[(size_t)(dimP + 2) * ld]);
+    const unsigned long long flag = 0x5A5A0001ull << 32;
+    double* red = &sA[0][0];                 // [8][32] partial sums
+    double* sLi = &sB[0][0];                 // L_kk^-1, row-major stride 33
+    for (int t = tid; t < kTile * kTile; t += kSolveThreads)
+      sB[t >> 5][t & 31] = __ldcg(&a.linv[(size_t)kb * kTile * kTile + t]);
+    if (tid < kTile) s_x[kb * kTile + tid] = __ldcg(&H[(size_t)dimP * ld + kb * kTile + tid]);  // y_kb
+    const int c = tid & 31, rg = tid >> 5;   // column of the tile, group of 4 rows
+    double tile[4];
+    if (kb + 1 < nblk) {
+#pragma unroll
+      for (int q = 0; q < 4; q++) tile[q] = __ldcg(&H[(size_t)((nblk - 1) * kTile + rg * 4 + q) * ld + kb * kTile + c]);
+    }
+    __syncthreads();
+    for (int j = nblk - 1; j > kb; j--) {
+      double cur[4];
+#pragma unroll
+      for (int q = 0; q < 4; q++) cur[q] = tile[q];
+      if (j - 1 > kb) {  // next tile in flight while we wait for x_j
+#pragma unroll
+        for (int q = 0; q < 4; q++) tile[q] = __ldcg(&H[(size_t)((j - 1) * kTile + rg * 4 + q) * ld + kb * kTile + c]);
+      }
+      if (tid < 2 * kTile) {
+        unsigned long long wv;
+        const unsigned long long* src = xw + (size_t)j * 2 * kTile + tid;
+        while (true) {
+          asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(wv) : "l"(src) : "memory");
+          if ((wv >> 32) == (flag >> 32)) break;
+        }
+        reinterpret_cast<unsigned*>(&s_x[j * kTile])[tid] = (unsigned)wv;  // word 2r = low half, 2r+1 = high half
+      }
+      __syncthreads();
+      double part = 0.0;
+#pragma unroll
+      for (int q = 0; q < 4; q++) part += cur[q] * s_x[j * kTile + rg * 4 + q];
+      red[rg * kTile + c] = part;
+      __syncthreads();
+      if (tid < kTile) {
+        double sum = 0.0;
+#pragma unroll
+        for (int g = 0; g < kSolveThreads / 32; g++) sum += red[g * kTile + tid];
+        s_x[kb * kTile + tid] -= sum;
+      }
+      __syncthreads();
+    }
     double xv = 0.0;
+    if (tid < kTile)
+      for (int m = tid; m < kTile; m++) xv += sLi[m * (kTile + 1) + tid] * s_x[kb * kTile + m];
+    __syncthreads();
     if (tid < kTile) {
-      const double* Li = a.linv + (size_t)kb * kTile * kTile;
-      for (int m = tid; m < kTile; m++) xv += Li[m * kTile + tid] * s_x[kb * kTile + m];
+      s_x[kb * kTile + tid] = xv;
+      const unsigned long long bits = (unsigned long long)__double_as_longlong(xv);
+      unsigned long long* dst = xw + (size_t)kb * 2 * kTile + 2 * tid;
+      asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(dst), "l"(flag | (bits & 0xffffffffull)) : "memory");
+      asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(dst + 1), "l"(flag | (bits >> 32)) : "memory");
     }
     __syncthreads();
-    if (tid < kTile) s_x[kb * kTile + tid] = xv;
+    if (blockIdx.x != 0) return;
+  } else {
+    if (blockIdx.x != 0) return;
+    for (int t = tid; t < dimP; t += kSolveThreads) s_x[t] = __ldcg(&H[(size_t)dimP * ld + t]);  // y = L^-1 g
     __syncthreads();
-    // s[col] -= sum_r L[kb*32 + r][col] * x_kb[r]   for col < kb*32
-    for (int col = tid; col < kb * kTile; col += kSolveThreads) {
-      double s = 0.0;
+    for (int kb = nblk - 1; kb >= 0; kb--) {
+      // x_kb = L_kk^-T s_kb : x[c] = sum_{m >= c} Linv[m][c] * s[m]
+      double xv = 0.0;
+      if (tid < kTile) {
+        const double* Li = a.linv + (size_t)kb * kTile * kTile;
+        for (int m = tid; m < kTile; m++) xv += __ldcg(&Li[m * kTile + tid]) * s_x[kb * kTile + m];
+      }
+      __syncthreads();
+      if (tid < kTile) s_x[kb * kTile + tid] = xv;
+      __syncthreads();
+      // s[col] -= sum_r L[kb*32 + r][col] * x_kb[r]   for col < kb*32
+      for (int col = tid; col < kb * kTile; col += kSolveThreads) {
+        double s = 0.0;
 #pragma unroll 8
-      for (int r = 0; r < kTile; r++) s += __ldcg(&H[(size_t)(kb * kTile + r) * ld + col]) * s_x[kb * kTile + r];
-      s_x[col] -= s;
+        for (int r = 0; r < kTile; r++) s += __ldcg(&H[(size_t)(kb * kTile + r) * ld + col]) * s_x[kb * kTile + r];
+        s_x[col] -= s;
+      }
+      __syncthreads();
     }
-    __syncthreads();
   }
 
   SLV(5);

@@ -113,9 +113,9 @@ def test_tracking_sized_full_resolution_vs_reference_cuda(backends, ref_backends
     assert rel < REL_TOL and ang < ANG_TOL
 
 
-@pytest.mark.parametrize("N,E", [(12, 20), (40, 90)])
+@pytest.mark.parametrize("N,E", [(12, 20), (40, 90), (64, 160)])
 def test_cooperative_solver_sizes(backends, oracle, synth, N, E):
-    """dim 77 (3 tiles) and 273 (9 tiles): the multi-CTA Cholesky path"""
+    """dim 77 (3 tiles), 273 (9 tiles) and 441 (14 tiles: look-ahead factorisation): the multi-CTA Cholesky path"""
     need_gpu()
     g = _cuda(synth.make_graph_exact(N, E, 1500, seed=N, noise=1e-3))
     Twc, dx = _run(backends, "rays", g)
