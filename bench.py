@@ -362,6 +362,12 @@ def run_gpu(args):
     if args.global_opt != "none":
         gopt = run_global_opt(args, abi, synth, mdist, dev, rank, world, barrier, max_over_ranks, peak)
 
+    # ---- factor-graph staging, one GPU ---------------------------------------
+    fgraph = None
+    if args.global_opt == "c3" and world == 1:
+        torch.cuda.empty_cache()
+        fgraph = run_factor_graph(abi, synth, dev, peak)
+
     # ---- CPU baseline on rank 0 at N=1 --------------------------------------------------------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -378,7 +384,7 @@ def run_gpu(args):
                            "parallelism": f"replicas x{world}" if world > 1 else "1 GPU"},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * K,
                 "roofline": roofline, "kernels": kern, "cpu_baseline": cpu, "global_opt": gopt,
-                "match_pipeline": match_pipeline}
+                "match_pipeline": match_pipeline, "factor_graph": fgraph}
         emit(line)
     if world > 1:
         dist.destroy_process_group()
@@ -467,6 +473,131 @@ def run_global_opt(args, abi, synth, mdist, dev, rank, world, barrier, max_over_
             "collective": "ncclAllReduce(sum, f64) of the [E2,56] edge blocks, once per iteration" if world > 1 else None,
             "max_abs_pose_err_vs_gt": gerr,
             "working_set": "13 B/pt/edge slabs (>= 0.6 GB per rank at c3/8) exceed the 126 MB L2; not flushed"}
+
+
+def run_factor_graph(abi, synth, dev, peak):
+    """Config-3 graph fed pair by pair into the device-resident FactorGraph (factor_graph.py), against a torch
+    restatement of the reference's staging (global_opt.py:54-58, 89-96, 104-119) on the same GPU."""
+    import torch
+    fgm = importlib.import_module("monst3r-slam_b200.factor_graph")
+    N, E, batch = 32, 120, 8
+    g = synth.make_graph(N, E, H, W, seed=1003, device=dev, calib=False)
+    n = N_PX
+    frames = fgm.KeyframeBuffer(n, capacity=N, device=dev)
+    for k in range(N):
+        frames.append(g["Xs"][k], g["Cs"][k], g["Twc"][k])
+    ones = torch.ones((batch, n, 1), dtype=torch.float32, device=dev)
+    Q2 = g["Q"] ** 2
+    feeds = []
+    for lo in range(0, E, batch):
+        hi = min(lo + batch, E)
+        feeds.append((g["ii"][lo:hi].tolist(), g["jj"][lo:hi].tolist(),
+                      (g["idx"][lo:hi], g["idx"][E + lo:E + hi], g["valid"][lo:hi], g["valid"][E + lo:E + hi],
+                       ones[:hi - lo], ones[:hi - lo], Q2[lo:hi], Q2[E + lo:E + hi])))
+
+    def ev():
+        return torch.cuda.Event(enable_timing=True)
+
+    # (1) admit kernel alone: all 15 batches back to back into a scratch store (1.4 GB of cold inputs)
+    st = fgm.EdgeStore(n, E, dev)
+    t_admit = []
+    for rep in range(4):
+        a, b = ev(), ev()
+        a.record()
+        for k, (_, _, m) in enumerate(feeds):
+            abi.edge_admit(*m, 1.5, st.idx, st.valid, st.Q, k * batch)
+        b.record()
+        b.synchronize()
+        if rep:
+            t_admit.append(a.elapsed_time(b))
+    admit_ms = statistics.median(t_admit)
+    admit_bytes = 2 * E * n * 30
+    # ... and as ONE launch over all 120 pairs (no launch gaps: the kernel's own bandwidth)
+    one = (g["idx"][:E], g["idx"][E:], g["valid"][:E], g["valid"][E:], torch.ones((E, n, 1), dtype=torch.float32, device=dev),
+           torch.ones((E, n, 1), dtype=torch.float32, device=dev), Q2[:E], Q2[E:])
+    t_one = []
+    for rep in range(4):
+        a, b = ev(), ev()
+        a.record()
+        abi.edge_admit(*one, 1.5, st.idx, st.valid, st.Q, 0)
+        b.record()
+        b.synchronize()
+        if rep:
+            t_one.append(a.elapsed_time(b))
+    admit_one_ms = statistics.median(t_one)
+    del st, one
+    # (2) add_factors end to end (kernel + accept/reject bookkeeping + its one host sync), growth from capacity 8
+    add_ms = {}
+    for cap in (8, E, E):  # growth from 8 pairs (cudaMalloc + copies); preallocated (second run: warm)
+        fg = fgm.FactorGraph(frames=frames, device=dev, capacity=cap, cfg={"delta_norm": 0.0})
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for f_ii, f_jj, m in feeds:
+            fg.add_factors_from_matches(f_ii, f_jj, m, 0.1)
+        torch.cuda.synchronize()
+        add_ms[cap] = (time.perf_counter() - t0) * 1e3
+        if cap == 8:
+            grown = fg.store.moved_bytes
+            del fg
+            torch.cuda.empty_cache()
+    E_acc = fg.num_edges
+    # (3) per-solve staging: zero-copy views vs the reference's cat/stack statements
+    ref_parts = [fg.ii.clone(), fg.jj.clone(), fg.idx_ii2jj.contiguous(), fg.idx_jj2ii.contiguous(),
+                 fg.valid_match_j.contiguous(), fg.valid_match_i.contiguous(), fg.Q_ii2jj.contiguous(),
+                 fg.Q_jj2ii.contiguous()]
+    kf_X = [frames.X_canon[k].clone() for k in range(N)]
+    kf_C = [frames.C[k].clone() for k in range(N)]
+    kf_T = [frames.T_WC[k].clone() for k in range(N)]
+
+    def stage_reference():
+        r_ii, r_jj, i1, i2, v1, v2, q1, q2 = ref_parts
+        torch.unique(torch.cat([r_ii, r_jj]), sorted=True)
+        out = (torch.stack(kf_X), torch.stack(kf_T), torch.stack(kf_C), torch.cat((r_ii, r_jj)), torch.cat((r_jj, r_ii)),
+               torch.cat((i1, i2)), torch.cat((v1, v2)), torch.cat((q1, q2)))
+        return out
+
+    def stage_store():
+        u = fg.get_unique_kf_idx()
+        return fg.get_poses_points(u), fg.prep_two_way_edges()
+
+    def timed(fn, reps=5):
+        ts = []
+        for r in range(reps + 2):
+            a, b = ev(), ev()
+            torch.cuda.synchronize()
+            t = time.perf_counter()
+            a.record()
+            out = fn()
+            b.record()
+            b.synchronize()
+            wall = (time.perf_counter() - t) * 1e3
+            del out
+            if r >= 2:
+                ts.append(max(a.elapsed_time(b), wall))
+        return statistics.median(ts)
+
+    stage_ref_ms = timed(stage_reference)
+    stage_store_ms = timed(stage_store)
+    pose0 = frames.T_WC.clone()
+
+    def solve():
+        frames.T_WC.copy_(pose0)
+        fg.solve_GN_rays()
+
+    solve_ms = timed(solve)
+    gerr = float((frames.T_WC[:N] - g["Twc_gt"]).abs().max().item())
+    return {"what": "SURVEY 8(f) rank 2: config-3 graph (32 kf) fed in batches of 8 pairs to the device-resident FactorGraph",
+            "pairs_offered": E, "pairs_accepted": E_acc, "edge_admit_ms_total": admit_ms,
+            "edge_admit_GBps": admit_bytes / (admit_ms * 1e-3) / 1e9,
+            "edge_admit_frac_of_hbm_peak": admit_bytes / (admit_ms * 1e-3) / 1e9 / peak,
+            "edge_admit_bytes": admit_bytes, "edge_admit_bytes_per_pt": 30,
+            "edge_admit_single_launch_ms": admit_one_ms,
+            "edge_admit_single_launch_GBps": admit_bytes / (admit_one_ms * 1e-3) / 1e9,
+            "edge_admit_single_launch_frac_of_hbm_peak": admit_bytes / (admit_one_ms * 1e-3) / 1e9 / peak,
+            "add_factors_wall_ms_15_batches_preallocated": add_ms[E], "add_factors_wall_ms_15_batches_growing_from_8": add_ms[8],
+            "store_growth_bytes_moved": grown,
+            "per_solve_staging_ms_reference_cat_stack": stage_ref_ms, "per_solve_staging_ms_store_views": stage_store_ms,
+            "solve_GN_rays_ms_through_store": solve_ms, "max_abs_pose_err_vs_gt": gerr}
 
 
 # ------------------------------------------------------------------------------------------ CPU arm

@@ -174,6 +174,26 @@ int m3r_gn_export_hs_gs(const void* workspace, int num_kf, int num_edges, int nu
 /* pose retraction alone: T_k <- exp(dx[k-num_fix]) * T_k for k >= num_fix (gn_kernels.cu:415-453) */
 int m3r_pose_retr(float* Twc, const float* dx, int num_kf, int num_fix, void* stream);
 
+/* ---- factor-graph staging (additive) -------------------------
+ * m3r_edge_admit replaces the tensor arithmetic of FactorGraph.add_factors that follows the symmetric
+ * matcher (mast3r_slam/global_opt.py:54-67) and the slab growth by torch.cat (:89-96, :104-110).
+ * For each of `batch` new keyframe pairs b and both directions it computes
+ *     Q[k] = sqrt(Q_src[b, idx[b,k]] * Q_dst[b,k])      dir 0: idx_i2j, Qii, Qji   dir 1: idx_j2i, Qjj, Qij
+ * writes {idx, valid, Q} into the caller's edge-store slabs (row-major [2*capacity, num_pts]) at
+ * directed slot 2*(slot0+b)+dir, and counts_out[2*b+dir] = #{k: valid && Q > Q_conf} (the numerator
+ * of match_frac; the accept/reject decision of :69-76 stays with the host).  The slabs are laid out
+ * exactly as m3r_gauss_newton's idx / valid / Q arguments, so a solve reads them in place.
+ * All inputs [batch, num_pts] contiguous; int32 counts_out[2*batch] is zeroed by the call. */
+int m3r_edge_admit(const int64_t* idx_i2j, const int64_t* idx_j2i, const uint8_t* valid_j, const uint8_t* valid_i,
+                   const float* Qii, const float* Qjj, const float* Qji, const float* Qij, int batch, int num_pts,
+                   float Q_conf, int64_t* store_idx, uint8_t* store_valid, float* store_Q, int64_t slot0,
+                   int32_t* counts_out, void* stream);
+
+/* constrain_points_to_ray (mast3r_slam/geometry.py:37-42, :107-114): out[kf,k] = z * ((u-cx)/fx, (v-cy)/fy, 1)
+ * with z = Xs[kf,k,2], u = k mod width, v = k div width, K row-major 3x3 on the device.  out may alias Xs. */
+int m3r_constrain_points_to_ray(const float* Xs, float* out, const float* K, int num_kf, int height, int width,
+                                void* stream);
+
 /* ---- NCCL plumbing (resolved with dlopen; no link-time dependency) ------------------------ */
 #define M3R_NCCL_UNIQUE_ID_BYTES 128
 int m3r_comm_unique_id(void* id_out /* 128 bytes, host */);

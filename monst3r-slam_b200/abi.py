@@ -24,7 +24,7 @@ EXPORTS = [
     "m3r_refine_matches_f32", "m3r_refine_matches_f64", "m3r_gn_workspace_bytes", "m3r_gn_workspace_bytes_sharded",
     "m3r_gauss_newton", "m3r_gn_prepare", "m3r_gn_pack", "m3r_gn_accumulate", "m3r_gn_edge_blocks", "m3r_gn_solve_retract",
     "m3r_gn_export_hs_gs", "m3r_pose_retr", "m3r_comm_unique_id", "m3r_comm_init", "m3r_comm_destroy",
-    "m3r_comm_allreduce_f64",
+    "m3r_comm_allreduce_f64", "m3r_edge_admit", "m3r_constrain_points_to_ray",
 ]
 
 
@@ -269,3 +269,43 @@ def comm_init(rank, world, uid):
 
 def comm_destroy(comm):
     _check(lib.m3r_comm_destroy(comm), "m3r_comm_destroy")
+
+
+def edge_admit(idx_i2j, idx_j2i, valid_j, valid_i, Qii, Qjj, Qji, Qij, Q_conf, store_idx, store_valid, store_Q, slot0):
+    """m3r_edge_admit: Q of both directions of `batch` new pairs written into the store slabs at undirected
+    slots slot0.., returns int32 counts [batch, 2] of (valid & Q > Q_conf).  global_opt.py:54-67, :89-96."""
+    batch, n = idx_i2j.shape[0], idx_i2j.shape[1]
+    for t, nm in ((idx_i2j, "idx_i2j"), (idx_j2i, "idx_j2i")):
+        _req(t, nm, torch.int64)
+    for t, nm in ((valid_j, "valid_match_j"), (valid_i, "valid_match_i")):
+        _req(t, nm, torch.bool)
+    for t, nm in ((Qii, "Qii"), (Qjj, "Qjj"), (Qji, "Qji"), (Qij, "Qij"), (store_Q, "store_Q")):
+        _req(t, nm, torch.float32)
+    _req(store_idx, "store_idx", torch.int64)
+    _req(store_valid, "store_valid", torch.bool)
+    for t in (idx_j2i, valid_j, valid_i, Qii, Qjj, Qji, Qij):
+        if t.numel() != batch * n:
+            raise M3RError("edge_admit: every input must hold batch x num_pts elements")
+    if store_idx.shape[-1] != n or 2 * (slot0 + batch) > store_idx.shape[0]:
+        raise M3RError("edge_admit: store slabs too small for this batch")
+    counts = torch.empty((batch, 2), dtype=torch.int32, device=idx_i2j.device)
+    _check(lib.m3r_edge_admit(_ptr(idx_i2j), _ptr(idx_j2i), _ptr(valid_j), _ptr(valid_i), _ptr(Qii), _ptr(Qjj),
+                              _ptr(Qji), _ptr(Qij), int(batch), int(n), C.c_float(Q_conf), _ptr(store_idx),
+                              _ptr(store_valid), _ptr(store_Q), C.c_int64(slot0), _ptr(counts), _stream()),
+           "m3r_edge_admit")
+    return counts
+
+
+def constrain_points_to_ray(img_size, Xs, K, out=None):
+    """geometry.py:37-42 on [N, h*w, 3] (or [N, h, w, 3]) float32 CUDA points."""
+    h, w = int(img_size[0]), int(img_size[1])
+    _req(Xs, "Xs", torch.float32)
+    _req(K, "K", torch.float32)
+    if Xs.numel() % (h * w * 3) != 0:
+        raise M3RError("constrain_points_to_ray: Xs does not hold whole h x w x 3 maps")
+    num = Xs.numel() // (h * w * 3)
+    if out is None:
+        out = torch.empty_like(Xs)
+    _check(lib.m3r_constrain_points_to_ray(_ptr(Xs), _ptr(out), _ptr(K), int(num), h, w, _stream()),
+           "m3r_constrain_points_to_ray")
+    return out
