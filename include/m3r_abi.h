@@ -194,6 +194,34 @@ int m3r_edge_admit(const int64_t* idx_i2j, const int64_t* idx_j2i, const uint8_t
 int m3r_constrain_points_to_ray(const float* Xs, float* out, const float* K, int num_kf, int height, int width,
                                 void* stream);
 
+/* ---- frame tracker pose optimisation (additive) -------------------------
+ * Replaces FrameTracker.opt_pose_ray_dist_sim3 / opt_pose_calib_sim3 and FrameTracker.solve
+ * (mast3r_slam/tracker.py:141-154, :156-214, :216-270) with one persistent cooperative launch.
+ *   T_WCf  [8] in/out  frame pose (t, q=xyzw, s); on return T_WCk * T_CkCf        (:192, :267)
+ *   T_CkCf_out [8]     optimised relative pose (may be NULL)
+ *   Xf [n,3]           frame points ALREADY gathered by idx_f2k (what get_points_poses returns, :139)
+ *   Xk [n,3]           keyframe points; valid [n] = valid_opt (:67); Q [n] = Qk (:41)
+ *   kind               M3R_GN_RAYS (sigma_a = sigma_ray, sigma_b = sigma_dist) or
+ *                      M3R_GN_CALIB (sigma_a = sigma_pixel, sigma_b = sigma_depth; K, height, width,
+ *                      pixel_border, z_eps = depth_eps; Xf / Xk constrained to their rays by the caller)
+ *   stop tests         after each update: |tau| < delta_norm  or  |old_cost - new_cost| / old_cost < rel_error
+ *                      (nonlinear_optimizer.py:5-26), at most max_iter iterations
+ *   dx_out [7]         last update; info_out int32[4] = {iterations, cholesky failures, stopped early, 0}
+ * A Cholesky failure leaves the pose of that iteration unchanged and is counted in info_out[1] (the reference
+ * raises and skips the frame, tracker.py:92-94: the host mirror does the same from info_out). */
+typedef struct m3r_track_params {
+  int kind;
+  float sigma_a, sigma_b;
+  int max_iter;
+  float rel_error, delta_norm, huber; /* huber must be 1.345 */
+  int height, width, pixel_border;
+  float z_eps;
+} m3r_track_params;
+size_t m3r_track_workspace_bytes(int num_pts);
+int m3r_track_frame(float* T_WCf, float* T_CkCf_out, const float* T_WCk, const float* Xf, const float* Xk,
+                    const uint8_t* valid, const float* Q, const float* K, int num_pts, const m3r_track_params* params,
+                    float* dx_out, int32_t* info_out, void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- NCCL plumbing (resolved with dlopen; no link-time dependency) ------------------------ */
 #define M3R_NCCL_UNIQUE_ID_BYTES 128
 int m3r_comm_unique_id(void* id_out /* 128 bytes, host */);

@@ -25,6 +25,7 @@ EXPORTS = [
     "m3r_gauss_newton", "m3r_gn_prepare", "m3r_gn_pack", "m3r_gn_accumulate", "m3r_gn_edge_blocks", "m3r_gn_solve_retract",
     "m3r_gn_export_hs_gs", "m3r_pose_retr", "m3r_comm_unique_id", "m3r_comm_init", "m3r_comm_destroy",
     "m3r_comm_allreduce_f64", "m3r_edge_admit", "m3r_constrain_points_to_ray",
+    "m3r_track_frame", "m3r_track_workspace_bytes",
 ]
 
 
@@ -33,6 +34,12 @@ class GnParams(C.Structure):
                 ("C_thresh", C.c_float), ("Q_thresh", C.c_float), ("max_iter", C.c_int),
                 ("delta_thresh", C.c_float), ("height", C.c_int), ("width", C.c_int),
                 ("pixel_border", C.c_int), ("z_eps", C.c_float)]
+
+
+class TrackParams(C.Structure):
+    _fields_ = [("kind", C.c_int), ("sigma_a", C.c_float), ("sigma_b", C.c_float), ("max_iter", C.c_int),
+                ("rel_error", C.c_float), ("delta_norm", C.c_float), ("huber", C.c_float), ("height", C.c_int),
+                ("width", C.c_int), ("pixel_border", C.c_int), ("z_eps", C.c_float)]
 
 
 class GnShard(C.Structure):
@@ -54,6 +61,8 @@ def _load():
     lib.m3r_gn_workspace_bytes.argtypes = [C.c_int, C.c_int, C.c_int]
     lib.m3r_gn_workspace_bytes_sharded.restype = C.c_size_t
     lib.m3r_gn_workspace_bytes_sharded.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int]
+    lib.m3r_track_workspace_bytes.restype = C.c_size_t
+    lib.m3r_track_workspace_bytes.argtypes = [C.c_int]
     return lib
 
 
@@ -309,3 +318,27 @@ def constrain_points_to_ray(img_size, Xs, K, out=None):
     _check(lib.m3r_constrain_points_to_ray(_ptr(Xs), _ptr(out), _ptr(K), int(num), h, w, _stream()),
            "m3r_constrain_points_to_ray")
     return out
+
+
+def track_frame(T_WCf, T_WCk, Xf, Xk, valid, Q, K, params, workspace=None):
+    """m3r_track_frame (tracker.py:156-270 in one launch).  T_WCf [8] / [1,8] f32 is updated in place.
+    Xf: frame points already gathered by idx_f2k.  -> (T_CkCf [8], dx [7], info int32[4] device tensors)"""
+    for t, nm, dt in ((T_WCf, "T_WCf", torch.float32), (T_WCk, "T_WCk", torch.float32), (Xf, "Xf", torch.float32),
+                      (Xk, "Xk", torch.float32), (valid, "valid", torch.bool), (Q, "Q", torch.float32)):
+        _req(t, nm, dt)
+    if K is not None:
+        _req(K, "K", torch.float32)
+    n = Xk.numel() // 3
+    if Xf.numel() != 3 * n or valid.numel() != n or Q.numel() != n or T_WCf.numel() != 8 or T_WCk.numel() != 8:
+        raise M3RError("track_frame: Xf/Xk [n,3], valid/Q [n], poses [8] expected")
+    dev = Xk.device
+    if workspace is None:
+        nbytes = int(lib.m3r_track_workspace_bytes(n))
+        workspace = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    T_rel = torch.empty(8, dtype=torch.float32, device=dev)
+    dx = torch.empty(7, dtype=torch.float32, device=dev)
+    info = torch.empty(4, dtype=torch.int32, device=dev)
+    _check(lib.m3r_track_frame(_ptr(T_WCf), _ptr(T_rel), _ptr(T_WCk), _ptr(Xf), _ptr(Xk), _ptr(valid), _ptr(Q), _ptr(K),
+                               int(n), C.byref(params), _ptr(dx), _ptr(info), _ptr(workspace),
+                               C.c_size_t(workspace.numel()), _stream()), "m3r_track_frame")
+    return T_rel, dx, info

@@ -43,7 +43,8 @@ __host__ __device__ constexpr int tri(int a, int b) { return a * 7 - a * (a - 1)
 
 // acc[0..27] += w * J J^T (upper triangle), acc[28..34] += w * r * J ; MASK = non-zero columns of J
 template <unsigned MASK>
-__device__ __forceinline__ void rank1(float (&acc)[kAcc], const float (&J)[7], float w, float r) {
+__device__ __forceinline__ void rank1(float (&acc)[kAcc], const float (&J)[7], float w, float r,
+                                      float* cost = nullptr) {
   float wJ[7];
 #pragma unroll
   for (int a = 0; a < 7; a++)
@@ -61,6 +62,7 @@ __device__ __forceinline__ void rank1(float (&acc)[kAcc], const float (&J)[7], f
 #pragma unroll
   for (int a = 0; a < 7; a++)
     if ((MASK >> a) & 1u) acc[28 + a] = fmaf(wr, J[a], acc[28 + a]);
+  if (cost) *cost = fmaf(wr, r, *cost);  // sum of (robust sqrt-info * r)^2: the frame tracker's cost (x2)
 }
 
 __device__ __forceinline__ float huber(float x) {
@@ -83,7 +85,7 @@ struct AccumParams {
 template <int KIND>
 __device__ __forceinline__ void accum_point(float (&acc)[kAcc], const EdgeXform& X, const AccumParams& prm,
                                             float xjx, float xjy, float xjz, float sq, int mi,
-                                            float xix, float xiy, float xiz) {
+                                            float xix, float xiy, float xiz, float* cost = nullptr) {
   bool ok = true;
   const float px = fmaf(X.m[0], xjx, fmaf(X.m[1], xjy, fmaf(X.m[2], xjz, X.t[0])));
   const float py = fmaf(X.m[3], xjx, fmaf(X.m[4], xjy, fmaf(X.m[5], xjz, X.t[1])));
@@ -95,15 +97,15 @@ __device__ __forceinline__ void accum_point(float (&acc)[kAcc], const EdgeXform&
     const float e0 = px - xix, e1 = py - xiy, e2 = pz - xiz;
     {
       const float J[7] = {1.f, 0.f, 0.f, 0.f, pz, -py, px};
-      rank1<0x71u>(acc, J, huber(sw * e0) * wc, e0);
+      rank1<0x71u>(acc, J, huber(sw * e0) * wc, e0, cost);
     }
     {
       const float J[7] = {0.f, 1.f, 0.f, -pz, 0.f, px, py};
-      rank1<0x6Au>(acc, J, huber(sw * e1) * wc, e1);
+      rank1<0x6Au>(acc, J, huber(sw * e1) * wc, e1, cost);
     }
     {
       const float J[7] = {0.f, 0.f, 1.f, py, -px, 0.f, pz};
-      rank1<0x5Cu>(acc, J, huber(sw * e2) * wc, e2);
+      rank1<0x5Cu>(acc, J, huber(sw * e2) * wc, e2, cost);
     }
   } else if (KIND == M3R_GN_RAYS) {
     const float n2j = fmaf(px, px, fmaf(py, py, pz * pz));
@@ -122,19 +124,19 @@ __device__ __forceinline__ void accum_point(float (&acc)[kAcc], const EdgeXform&
     const float xy = -rx * ry * inv_j, xz = -rx * rz * inv_j, yz = -ry * rz * inv_j;
     {
       const float J[7] = {xx, xy, xz, 0.f, rz, -ry, 0.f};
-      rank1<0x37u>(acc, J, huber(swr * e0) * wr, e0);
+      rank1<0x37u>(acc, J, huber(swr * e0) * wr, e0, cost);
     }
     {
       const float J[7] = {xy, yy, yz, -rz, 0.f, rx, 0.f};
-      rank1<0x2Fu>(acc, J, huber(swr * e1) * wr, e1);
+      rank1<0x2Fu>(acc, J, huber(swr * e1) * wr, e1, cost);
     }
     {
       const float J[7] = {xz, yz, zz, ry, -rx, 0.f, 0.f};
-      rank1<0x1Fu>(acc, J, huber(swr * e2) * wr, e2);
+      rank1<0x1Fu>(acc, J, huber(swr * e2) * wr, e2, cost);
     }
     {
       const float J[7] = {rx, ry, rz, 0.f, 0.f, 0.f, rho};
-      rank1<0x47u>(acc, J, huber(swd * e3) * wd, e3);
+      rank1<0x47u>(acc, J, huber(swd * e3) * wd, e3, cost);
     }
   } else {  // calib
     const bool vz = (pz > prm.z_eps) && (xiz > prm.z_eps);
@@ -151,16 +153,16 @@ __device__ __forceinline__ void accum_point(float (&acc)[kAcc], const EdgeXform&
     {
       const float J[7] = {prm.fx * zinv, 0.f, -prm.fx * xz_ * zinv, -prm.fx * xz_ * yz_,
                           prm.fx * fmaf(xz_, xz_, 1.f), -prm.fx * yz_, 0.f};
-      rank1<0x3Du>(acc, J, huber(swp * e0) * wp, e0);
+      rank1<0x3Du>(acc, J, huber(swp * e0) * wp, e0, cost);
     }
     {
       const float J[7] = {0.f, prm.fy * zinv, -prm.fy * yz_ * zinv, -prm.fy * fmaf(yz_, yz_, 1.f),
                           prm.fy * xz_ * yz_, prm.fy * xz_, 0.f};
-      rank1<0x3Eu>(acc, J, huber(swp * e1) * wp, e1);
+      rank1<0x3Eu>(acc, J, huber(swp * e1) * wp, e1, cost);
     }
     {
       const float J[7] = {0.f, 0.f, zinv, yz_, -xz_, 0.f, 1.f};
-      rank1<0x5Cu>(acc, J, huber(swd * e2) * wd, e2);
+      rank1<0x5Cu>(acc, J, huber(swd * e2) * wd, e2, cost);
     }
   }
 }
@@ -237,7 +239,8 @@ struct PackArgs {
 __device__ __forceinline__ bool pack_one(long long m, bool vm, float q, float cj, const float* __restrict__ Ci,
                                          float C_thresh, float Q_thresh, uint2& rec) {
   // invalid matches read C_i[0] in the reference (gn_kernels.cu:913-914); the result is discarded
-  const float ci = __ldg(Ci + (vm ? m : 0));
+  // (Ci == nullptr: frame-tracker mode, the caller's valid mask already holds every confidence test)
+  const float ci = Ci ? __ldg(Ci + (vm ? m : 0)) : INFINITY;
   rec = make_uint2((unsigned)(int)m, __float_as_uint(sqrtf(q)));
   return vm & (q > Q_thresh) & (ci > C_thresh) & (cj > C_thresh);
 }
@@ -250,9 +253,10 @@ gn_pack_kernel(const PackArgs a) {
   const int e = a.e_lo + el;
   const int n = a.n;
   const int ic = a.ci[e], jc = a.cj[e];
-  const float* __restrict__ Ci = a.Cs + (size_t)ic * n;
-  const float* __restrict__ Cj = a.Cs + (size_t)jc * n;
-  const int64_t* __restrict__ idx = a.idx + (size_t)el * n;
+  const bool track = a.Cs == nullptr;  // frame-tracker mode: identity index, no confidence maps
+  const float* __restrict__ Ci = track ? nullptr : a.Cs + (size_t)ic * n;
+  const float* __restrict__ Cj = track ? nullptr : a.Cs + (size_t)jc * n;
+  const int64_t* __restrict__ idx = track ? nullptr : a.idx + (size_t)el * n;
   const uint8_t* __restrict__ valid = a.valid + (size_t)el * n;
   const float* __restrict__ Q = a.Q + (size_t)el * n;
   const int p_lo = chunk * a.chunk_pts;
@@ -268,10 +272,14 @@ gn_pack_kernel(const PackArgs a) {
       bool ok[4] = {false, false, false, false};
       if (VEC4 && k0 + 3 < p_hi) {
         const uchar4 vm = __ldcs(reinterpret_cast<const uchar4*>(valid + k0));
-        const longlong2 m01 = __ldcs(reinterpret_cast<const longlong2*>(idx + k0));
-        const longlong2 m23 = __ldcs(reinterpret_cast<const longlong2*>(idx + k0) + 1);
+        longlong2 m01 = make_longlong2(k0, k0 + 1), m23 = make_longlong2(k0 + 2, k0 + 3);
+        float4 c4 = make_float4(INFINITY, INFINITY, INFINITY, INFINITY);
+        if (!track) {
+          m01 = __ldcs(reinterpret_cast<const longlong2*>(idx + k0));
+          m23 = __ldcs(reinterpret_cast<const longlong2*>(idx + k0) + 1);
+          c4 = __ldg(reinterpret_cast<const float4*>(Cj + k0));
+        }
         const float4 q4 = __ldcs(reinterpret_cast<const float4*>(Q + k0));
-        const float4 c4 = __ldg(reinterpret_cast<const float4*>(Cj + k0));
         ok[0] = pack_one(m01.x, vm.x != 0, q4.x, c4.x, Ci, a.C_thresh, a.Q_thresh, rec[0]);
         ok[1] = pack_one(m01.y, vm.y != 0, q4.y, c4.y, Ci, a.C_thresh, a.Q_thresh, rec[1]);
         ok[2] = pack_one(m23.x, vm.z != 0, q4.z, c4.z, Ci, a.C_thresh, a.Q_thresh, rec[2]);
@@ -281,7 +289,8 @@ gn_pack_kernel(const PackArgs a) {
         for (int r = 0; r < 4; r++) {
           const int k = k0 + r;
           if (k < p_hi)
-            ok[r] = pack_one(idx[k], valid[k] != 0, Q[k], __ldg(Cj + k), Ci, a.C_thresh, a.Q_thresh, rec[r]);
+            ok[r] = pack_one(track ? (long long)k : idx[k], valid[k] != 0, Q[k], track ? INFINITY : __ldg(Cj + k), Ci,
+                             a.C_thresh, a.Q_thresh, rec[r]);
         }
       }
       const int cnt = (int)ok[0] + (int)ok[1] + (int)ok[2] + (int)ok[3];
@@ -616,9 +625,14 @@ struct TrackArgs {
   int max_iter;
   int stage_pts;      // upc * chunk_pts
   unsigned epoch;     // per-launch nonce (20 bits) of the partial all-gather flags
+  // frame-tracker mode (COST): one directed edge whose two point sets are separate arrays, and the stop test of
+  // mast3r_slam/nonlinear_optimizer.py:5-26 on the relative decrease of the robust cost
+  const float* Xi_base;  // target points (keyframe), or nullptr: a.Xs + i*n*3
+  const float* Xj_base;  // moving points (frame, already gathered), or nullptr: a.Xs + j*n*3
+  float rel_error;
 };
 
-template <int KIND>
+template <int KIND, bool COST>
 __global__ void __launch_bounds__(kTrackThreads, 1)
 gn_track_kernel(const TrackArgs ta) {
   const AccumArgs& a = ta.a;
@@ -636,6 +650,8 @@ gn_track_kernel(const TrackArgs ta) {
   __shared__ TrackGraph s_g;
   __shared__ float s_dx[64];
   __shared__ int s_flags[2];
+  __shared__ float s_costw[kTrackThreads / 32];
+  __shared__ double s_cost[2];  // [0] this iteration's sum, [1] previous cost
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int E = a.e_local, n = a.n, N = a.ss.N;
@@ -688,7 +704,8 @@ gn_track_kernel(const TrackArgs ta) {
       const int npts = min(n, p_lo + a.chunk_pts) - p_lo;
       const uint32_t cnt8 = ((uint32_t)cnt + 7u) & ~7u;
       const uint32_t dst = smem_u32(dsm) + (uint32_t)u * slab;
-      bulk_g2s(dst, a.Xs + ((size_t)j * n + p_lo) * 3, (uint32_t)npts * 12u, bar, pol);
+      const float* Xj = ta.Xj_base ? ta.Xj_base : a.Xs + (size_t)j * n * 3;
+      bulk_g2s(dst, Xj + (size_t)p_lo * 3, (uint32_t)npts * 12u, bar, pol);
       bulk_g2s(dst + off_rec, a.packed + (size_t)e * n + p_lo, cnt8 * 8u, bar, pol);
       bulk_g2s(dst + off_k, a.kloc + (size_t)e * n + p_lo, cnt8 * 2u, bar, pol);
     }
@@ -696,7 +713,7 @@ gn_track_kernel(const TrackArgs ta) {
   mbar_wait(smem_u32(&s_bar), 0);
   // gather the matched points of frame i once (they do not depend on the poses)
   {
-    const float* __restrict__ Xi = a.Xs + (size_t)i * n * 3;
+    const float* __restrict__ Xi = ta.Xi_base ? ta.Xi_base : a.Xs + (size_t)i * n * 3;
     for (int u = 0; u < nu; u++) {
       const int cnt = s_cnt[u];
       const uint2* srec = reinterpret_cast<const uint2*>(dsm + (size_t)u * slab + off_rec);
@@ -735,6 +752,7 @@ gn_track_kernel(const TrackArgs ta) {
     float acc[kAcc];
 #pragma unroll
     for (int t = 0; t < kAcc; t++) acc[t] = 0.f;
+    float cost = 0.f;
     for (int u = 0; u < nu; u++) {
       const int cnt = s_cnt[u];
       const unsigned char* base = dsm + (size_t)u * slab;
@@ -746,10 +764,16 @@ gn_track_kernel(const TrackArgs ta) {
         const uint2 rec = srec[k];
         const float* xj = sx + (int)sk[k] * 3;
         const float* xi = sxi + k * 3;
-        accum_point<KIND>(acc, X, prm, xj[0], xj[1], xj[2], __uint_as_float(rec.y), (int)rec.x, xi[0], xi[1], xi[2]);
+        accum_point<KIND>(acc, X, prm, xj[0], xj[1], xj[2], __uint_as_float(rec.y), (int)rec.x, xi[0], xi[1], xi[2],
+                          COST ? &cost : nullptr);
       }
     }
     TRK(2);  // accumulate
+    if (COST) {
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) cost += __shfl_xor_sync(0xffffffffu, cost, off);
+      if (lane == 0) s_costw[warp] = cost;
+    }
     // CTA reduction (same transposing butterfly as gn_accum_kernel) -> fp64 partial of this CTA
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) {
@@ -778,6 +802,19 @@ gn_track_kernel(const TrackArgs ta) {
     // after that reader has consumed the older buffer.  The launch is cooperative (co-resident CTAs).
     ulonglong2* ll = reinterpret_cast<ulonglong2*>(a.partials) + (size_t)(it & 1) * gridDim.x * kAcc;
     const unsigned long long flag = ((unsigned long long)(ta.epoch << 12 | (unsigned)(it + 1))) << 32;
+    // (COST) the CTA's cost partial travels the same way, in its own words behind the pose words
+    ulonglong2* cost_ll = reinterpret_cast<ulonglong2*>(reinterpret_cast<unsigned long long*>(
+                              reinterpret_cast<ulonglong2*>(a.partials) + (size_t)2 * gridDim.x * kAcc) + 192) +
+                          (size_t)(it & 1) * gridDim.x;
+    if (COST && tid == kAcc) {
+      double s = 0.0;
+#pragma unroll
+      for (int wv = 0; wv < kTrackThreads / 32; wv++) s += (double)s_costw[wv];
+      const unsigned long long bits = (unsigned long long)__double_as_longlong(s);
+      asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(cost_ll + blockIdx.x),
+                   "l"(flag | (bits & 0xffffffffull)), "l"(flag | (bits >> 32))
+                   : "memory");
+    }
     if (tid < kAcc) {
       double s = 0.0;
 #pragma unroll
@@ -861,6 +898,19 @@ gn_track_kernel(const TrackArgs ta) {
       }
       s_part[sl][pr] = s;
     }
+    if (COST && warp == kTrackThreads / 32 - 1) {  // (E == 1: the last warp is free) cost partials, fixed order
+      double s = 0.0;
+      for (int c = lane; c < (int)gridDim.x; c += 32) {
+        ulonglong2 w;
+        do {
+          asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(w.x), "=l"(w.y) : "l"(cost_ll + c) : "memory");
+        } while ((w.x >> 32) != (flag >> 32) || (w.y >> 32) != (flag >> 32));
+        s += __longlong_as_double((long long)((w.x & 0xffffffffull) | (w.y << 32)));
+      }
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+      if (lane == 0) s_cost[0] = s;
+    }
     TRK(4);  // all-gather
 #ifdef M3R_TRACK_PROF
     if (it == 5 && tid == 0) {
@@ -933,6 +983,18 @@ gn_track_kernel(const TrackArgs ta) {
     TRK(6);  // adjoints
     track_solve(s_g, s_eb, s_pose, N, a.ss.dim, a.ss.delta_thresh, solve_sm, s_dx, s_flags);
     TRK(7);  // solve + retraction
+    if (COST) {
+      // nonlinear_optimizer.py:14-18 — after the update: |old - new| / old < rel_error (old = +inf at step 0: no stop)
+      if (tid == 0) {
+        const double new_cost = 0.5 * s_cost[0];
+        if (it > 0) {
+          const double rel_dec = fabs((s_cost[1] - new_cost) / s_cost[1]);
+          if (rel_dec < (double)ta.rel_error) s_flags[0] = 1;
+        }
+        s_cost[1] = new_cost;
+      }
+      __syncthreads();
+    }
     nfail += s_flags[1];
     const int stop = s_flags[0];
     {  // publish first (the other CTAs are waiting), then the plain stores of the outputs
@@ -972,16 +1034,16 @@ gn_track_kernel(const TrackArgs ta) {
   }
 }
 
-template <int KIND>
+template <int KIND, bool COST = false>
 int launch_track(const TrackArgs& ta, size_t dyn, cudaStream_t s) {
   static bool attr_done = false;
   if (!attr_done) {
-    M3R_CUDA_CHECK(cudaFuncSetAttribute(gn_track_kernel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    M3R_CUDA_CHECK(cudaFuncSetAttribute(gn_track_kernel<KIND, COST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         kTrackMaxPts * kTrackPtBytes + (int)small_solve_smem_bytes(kSmallDim)));
     attr_done = true;
   }
   void* params[] = {const_cast<TrackArgs*>(&ta)};
-  M3R_CUDA_CHECK(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(gn_track_kernel<KIND>),
+  M3R_CUDA_CHECK(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(gn_track_kernel<KIND, COST>),
                                              dim3(ta.a.e_local * ta.cpe), dim3(kTrackThreads), params, dyn, s));
   return M3R_OK;
 }
@@ -1122,8 +1184,9 @@ int launch_gn_accumulate(const float* Twc, const float* Xs, const float* K, cons
 // Whole GN loop in one cooperative launch (gn_track_kernel).  *launched = 0 when the problem is not
 // tracking-sized (the caller then runs the per-iteration path).
 int launch_gn_track(const float* Twc, const float* Xs, const float* K, const GnLayout& L, const GnPtrs& P,
-                    const m3r_gn_params& prm, const GnFuse& fuse, int* launched, cudaStream_t s) {
+                    const m3r_gn_params& prm, const GnFuse& fuse, int* launched, cudaStream_t s, const GnFrameTrack* ft) {
   *launched = 0;
+  if (ft && L.num_edges != 1) return M3R_ERR_BAD_ARG;
   const int E = L.num_edges;
   if (!fuse.enabled || E < 1 || E > kTrackMaxEdges || L.dim > kSmallDim || prm.max_iter < 1) return M3R_OK;
   static int num_sms = 0, coop = 0;
@@ -1137,10 +1200,16 @@ int launch_gn_track(const float* Twc, const float* Xs, const float* K, const GnL
   AccumArgs a;
   bool staged;
   size_t dyn;
-  int rc = fill_accum_args(a, staged, dyn, Twc, Xs, K, L, P, prm, 0, E, fuse);
+  int rc = fill_accum_args(a, staged, dyn, Twc, ft ? ft->Xj : Xs, K, L, P, prm, 0, E, fuse);
   if (rc != M3R_OK) return rc;
+  if (ft && (reinterpret_cast<uintptr_t>(ft->Xi) % 4 != 0)) return M3R_ERR_BAD_ARG;
   if (!staged || !a.fuse) return M3R_OK;
   TrackArgs ta{};
+  if (ft) {
+    ta.Xi_base = ft->Xi;
+    ta.Xj_base = ft->Xj;
+    ta.rel_error = ft->rel_error;
+  }
   ta.a = a;
   ta.cpe = std::min(a.chunks, num_sms / E);
   ta.upc = (a.chunks + ta.cpe - 1) / ta.cpe;
@@ -1149,15 +1218,24 @@ int launch_gn_track(const float* Twc, const float* Xs, const float* K, const GnL
   if (ta.upc > 64 || ta.stage_pts > kTrackMaxPts || prm.max_iter > 4095) return M3R_OK;
   // two gather buffers of grid x kAcc x 16 B + two pose buffers of 96 words live in P.partials
   // (gn_layout reserves >= (4 * 148 + 8) x kAcc doubles)
-  if ((size_t)4 * E * ta.cpe + 8 > std::max((size_t)E * a.chunks, (size_t)4 * kNumSMs + 8)) return M3R_OK;
+  // (+ two buffers of grid x 16 B of cost partials in frame-tracker mode)
+  if ((size_t)4 * E * ta.cpe + 32 > std::max((size_t)E * a.chunks, (size_t)4 * kNumSMs + 32)) return M3R_OK;
   static std::atomic<unsigned> g_epoch{1};
   ta.epoch = g_epoch.fetch_add(1) & 0xfffffu;
   const size_t dyn_track = (size_t)ta.stage_pts * kTrackPtBytes + small_solve_smem_bytes(L.dim);
-  switch (prm.kind) {
-    case M3R_GN_POINTS: rc = launch_track<M3R_GN_POINTS>(ta, dyn_track, s); break;
-    case M3R_GN_RAYS: rc = launch_track<M3R_GN_RAYS>(ta, dyn_track, s); break;
-    case M3R_GN_CALIB: rc = launch_track<M3R_GN_CALIB>(ta, dyn_track, s); break;
-    default: return M3R_ERR_BAD_ARG;
+  if (ft) {
+    switch (prm.kind) {
+      case M3R_GN_RAYS: rc = launch_track<M3R_GN_RAYS, true>(ta, dyn_track, s); break;
+      case M3R_GN_CALIB: rc = launch_track<M3R_GN_CALIB, true>(ta, dyn_track, s); break;
+      default: return M3R_ERR_BAD_ARG;
+    }
+  } else {
+    switch (prm.kind) {
+      case M3R_GN_POINTS: rc = launch_track<M3R_GN_POINTS>(ta, dyn_track, s); break;
+      case M3R_GN_RAYS: rc = launch_track<M3R_GN_RAYS>(ta, dyn_track, s); break;
+      case M3R_GN_CALIB: rc = launch_track<M3R_GN_CALIB>(ta, dyn_track, s); break;
+      default: return M3R_ERR_BAD_ARG;
+    }
   }
   if (rc == M3R_OK) *launched = 1;
   return rc;

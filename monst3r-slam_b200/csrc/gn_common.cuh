@@ -82,7 +82,7 @@ inline GnLayout gn_layout(int num_kf, int num_edges, int num_pts, int edges_loca
   L.off_inc_list = take(sizeof(int) * 2 * (size_t)num_edges);
   L.off_order = take(sizeof(int) * (size_t)num_edges);
   // (the persistent tracking kernel keeps two all-gather buffers of 16 B x kAcc per CTA of a <= 148-CTA grid here)
-  const size_t worst = std::max((size_t)num_edges * (size_t)gn_chunking(num_edges, num_pts).chunks, (size_t)4 * kNumSMs + 8);
+  const size_t worst = std::max((size_t)num_edges * (size_t)gn_chunking(num_edges, num_pts).chunks, (size_t)4 * kNumSMs + 32);
   L.off_partials = take(sizeof(double) * kAcc * worst);
   L.off_eb = take(sizeof(double) * kEdgeBlock * (size_t)num_edges);
   L.off_hd = take(sizeof(double) * (size_t)L.rows * L.ld);
@@ -154,8 +154,16 @@ int launch_gn_pack(const float* Cs, const int64_t* idx, const uint8_t* valid, co
                    const GnPtrs& P, const m3r_gn_params& prm, int e_lo, int e_hi, cudaStream_t s);
 int launch_gn_accumulate(const float* Twc, const float* Xs, const float* K, const GnLayout& L, const GnPtrs& P,
                          const m3r_gn_params& prm, int e_lo, int e_hi, const GnFuse& fuse, cudaStream_t s);
+// frame-tracker mode of the persistent kernel: one directed edge, target / moving points in separate arrays,
+// extra stop test on the relative decrease of the robust cost (tracker.py:156-214)
+struct GnFrameTrack {
+  const float* Xi;  // [n,3] keyframe points (targets)
+  const float* Xj;  // [n,3] frame points, already gathered by idx_f2k (moved by T_CkCf)
+  float rel_error;
+};
 int launch_gn_track(const float* Twc, const float* Xs, const float* K, const GnLayout& L, const GnPtrs& P,
-                    const m3r_gn_params& prm, const GnFuse& fuse, int* launched, cudaStream_t s);
+                    const m3r_gn_params& prm, const GnFuse& fuse, int* launched, cudaStream_t s,
+                    const GnFrameTrack* ft = nullptr);
 int launch_gn_solve(float* Twc, const GnLayout& L, const GnPtrs& P, float delta_thresh, float* dx_out,
                     int32_t* info_out, cudaStream_t s);
 int launch_export_hs_gs(const GnLayout& L, const GnPtrs& P, float* Hs, float* gs, cudaStream_t s);
