@@ -439,6 +439,11 @@ def run_gpu(args):
         torch.cuda.empty_cache()
         fgraph = run_factor_graph(abi, synth, dev, peak)
 
+    # ---- frame tracker pose optimisation, one GPU ------------------------------
+    ftrack = None
+    if world == 1:
+        ftrack = run_frame_tracker(synth, dev)
+
     # ---- CPU baseline on rank 0 at N=1 --------------------------------------------------------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -455,7 +460,7 @@ def run_gpu(args):
                            "parallelism": f"replicas x{world}" if world > 1 else "1 GPU"},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * K,
                 "roofline": roofline, "kernels": kern, "cpu_baseline": cpu, "global_opt": gopt,
-                "match_pipeline": match_pipeline, "factor_graph": fgraph}
+                "match_pipeline": match_pipeline, "factor_graph": fgraph, "frame_tracker": ftrack}
         emit(line)
     if world > 1:
         dist.destroy_process_group()
@@ -544,6 +549,108 @@ def run_global_opt(args, abi, synth, mdist, dev, rank, world, barrier, max_over_
             "collective": "ncclAllReduce(sum, f64) of the [E2,56] edge blocks, once per iteration" if world > 1 else None,
             "max_abs_pose_err_vs_gt": gerr,
             "working_set": "13 B/pt/edge slabs (>= 0.6 GB per rank at c3/8) exceed the 126 MB L2; not flushed"}
+
+
+def run_frame_tracker(synth, dev):
+    """FrameTracker.opt_pose_ray_dist_sim3 (tracker.py:156-214) at 512x384 with config/base.yaml's tracking thresholds:
+    one persistent launch (m3r_track_frame) vs a torch restatement of ONE iteration of the reference loop
+    (act_Sim3 + point_to_ray_dist Jacobians + FrameTracker.solve, tracker.py:141-154,169-176; lietorch is absent,
+    so the Sim(3) action is written out and the retraction is left out) on the same GPU."""
+    import torch
+    trk = importlib.import_module("monst3r-slam_b200.tracker")
+    g = synth.make_graph(2, 1, H, W, seed=1002, device=dev, calib=False)
+    e = 1  # ii = 1 (frame, gathered side), jj = 0 (keyframe)
+    Xf = g["Xs"][1][g["idx"][e]].contiguous()
+    Xk = g["Xs"][0].contiguous()
+    Q = g["Q"][e].reshape(-1, 1).contiguous()
+    valid = (g["valid"][e].reshape(-1, 1) & (Q > 1.5)).contiguous()
+    T_WCf, T_WCk = g["Twc"][1].reshape(1, 8).contiguous(), g["Twc"][0].reshape(1, 8).contiguous()
+    opt = trk.PoseOptimizer()
+
+    def ev():
+        return torch.cuda.Event(enable_timing=True)
+
+    def timed(fn, reps=10, warm=3):
+        ts, ws = [], []
+        for r in range(reps + warm):
+            a, b = ev(), ev()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            a.record()
+            fn()
+            b.record()
+            b.synchronize()
+            if r >= warm:
+                ws.append((time.perf_counter() - t0) * 1e3)
+                ts.append(a.elapsed_time(b))
+        return statistics.median(ts), statistics.median(ws)
+
+    out = {}
+
+    def ours():
+        out["T"], out["Trel"] = opt.opt_pose_ray_dist_sim3(Xf, Xk, T_WCf, T_WCk, Q, valid)
+
+    dev_ms, wall_ms = timed(ours)
+    iters = int(opt.last_info[0])
+    opt_async = trk.PoseOptimizer(sync_check=False)
+    dev_async_ms, _ = timed(lambda: opt_async.opt_pose_ray_dist_sim3(Xf, Xk, T_WCf, T_WCk, Q, valid))
+    gerr = float((out["T"].reshape(-1) - g["Twc_gt"][1]).abs().max().item())
+
+    # torch restatement of one reference iteration (fp32, the reference's statements)
+    c = opt.cfg
+    t_, q_, s_ = T_WCf[0, :3], T_WCf[0, 3:7], T_WCf[0, 7]
+    x, y, z, w = q_
+    R = torch.stack((1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w), 2 * (x * y + z * w),
+                     1 - 2 * (x * x + z * z), 2 * (y * z - x * w), 2 * (x * z - y * w), 2 * (y * z + x * w),
+                     1 - 2 * (x * x + y * y))).view(3, 3)
+    sqrt_info_ray = 1 / c["sigma_ray"] * valid * torch.sqrt(Q)
+    sqrt_info_dist = 1 / c["sigma_dist"] * valid * torch.sqrt(Q)
+    sqrt_info = torch.cat((sqrt_info_ray.repeat(1, 3), sqrt_info_dist), dim=1)
+
+    def rd(X, jac):
+        d = torch.linalg.norm(X, dim=-1, keepdim=True)
+        d_inv = 1.0 / d
+        r = d_inv * X
+        out_ = torch.cat((r, d), dim=-1)
+        if not jac:
+            return out_
+        I = torch.eye(3, device=X.device, dtype=X.dtype).repeat(X.shape[0], 1, 1)
+        dr = d_inv.unsqueeze(-1) * (I - (d_inv ** 2).unsqueeze(-1) * (X.unsqueeze(-1) @ X.unsqueeze(-2)))
+        return out_, torch.cat((dr, r.unsqueeze(-2)), dim=-2)
+
+    rd_k = rd(Xk, False)
+
+    def ref_iteration():
+        pW = s_ * (Xf @ R.T) + t_
+        o = torch.zeros_like(pW[:, 0])
+        sk = torch.stack([o, -pW[:, 2], pW[:, 1], pW[:, 2], o, -pW[:, 0], -pW[:, 1], pW[:, 0], o], dim=-1).view(-1, 3, 3)
+        dX = torch.cat([torch.eye(3, device=dev).repeat(pW.shape[0], 1, 1), -sk, pW.reshape(-1, 3, 1)], dim=-1)
+        rd_f, drd = rd(pW, True)
+        r = rd_k - rd_f
+        J = -drd @ dX
+        whitened = sqrt_info * r
+        r_abs = torch.abs(whitened)
+        wgt = torch.where(r_abs < c["huber"], torch.ones(1, device=dev), c["huber"] / r_abs)
+        robust = sqrt_info * torch.sqrt(wgt)
+        A = (robust[..., None] * J).view(-1, 7)
+        b = (robust * r).view(-1, 1)
+        Hm = A.T @ A
+        gv = -A.T @ b
+        cost = 0.5 * (b.T @ b).item()
+        L = torch.linalg.cholesky(Hm, upper=False)
+        return torch.cholesky_solve(gv, L, upper=False).view(1, -1), cost
+
+    ref_dev_ms, ref_wall_ms = timed(ref_iteration, reps=5, warm=2)
+    return {"what": "SURVEY 8(f) rank 3: FrameTracker.opt_pose_ray_dist_sim3 at 512x384, config/base.yaml tracking thresholds "
+                    "(rel_error 1e-3, delta_norm 1e-3, max_iters 50)",
+            "iterations": iters, "ms_per_frame": wall_ms, "device_ms_per_frame": dev_ms,
+            "device_ms_per_frame_without_info_readback": dev_async_ms, "launches_per_frame": 5,
+            "px_per_s": N_PX / (wall_ms * 1e-3),
+            "reference_torch_ms_per_iteration": ref_wall_ms, "reference_torch_device_ms_per_iteration": ref_dev_ms,
+            "reference_torch_ms_per_frame_estimate": ref_wall_ms * iters,
+            "reference_note": "torch restatement of ONE iteration of tracker.py:141-154,169-176 (no retraction; lietorch is "
+                              "absent) x the iterations our kernel executed",
+            "max_abs_pose_err_vs_gt": gerr}
 
 
 def run_factor_graph(abi, synth, dev, peak):
