@@ -35,6 +35,7 @@ struct AdmitArgs {
   int32_t* counts;          // [batch, 2]
   long long slot0;          // first undirected slot of this batch
   int n, batch;
+  int iters;  // 1024-point sub-chunks per CTA (host: fewer, longer-lived CTAs once the grid fills the SMs)
   float q_conf;
 };
 
@@ -57,28 +58,39 @@ __global__ void __launch_bounds__(kAdmitThreads) edge_admit_kernel(const AdmitAr
   uint8_t* __restrict__ o_valid = a.s_valid + out_off;
   float* __restrict__ o_q = a.s_q + out_off;
 
-  const int k0 = blockIdx.x * kAdmitChunk + threadIdx.x * kAdmitPerThread;
+  // A warp owns 128 consecutive points as two halves of 64: lane l takes points {2l, 2l+1} of each half, so every
+  // warp-wide load / store instruction covers whole, consecutive 32-byte sectors (16 B idx, 8 B Q, 2 B valid per lane).
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   int cnt = 0;
   const bool vec = (n % kAdmitPerThread) == 0;  // rows start 16-byte aligned only then
-  if (vec && k0 + kAdmitPerThread <= n) {
-    const longlong2 m01 = __ldcs(reinterpret_cast<const longlong2*>(idx + k0));
-    const longlong2 m23 = __ldcs(reinterpret_cast<const longlong2*>(idx + k0) + 1);
-    const uchar4 vm = __ldcs(reinterpret_cast<const uchar4*>(valid + k0));
-    const float4 q4 = __ldcs(reinterpret_cast<const float4*>(qd + k0));
-    float4 q;
-    q.x = admit_q(qs, m01.x, n, q4.x);
-    q.y = admit_q(qs, m01.y, n, q4.y);
-    q.z = admit_q(qs, m23.x, n, q4.z);
-    q.w = admit_q(qs, m23.y, n, q4.w);
-    cnt = (vm.x != 0 && q.x > a.q_conf) + (vm.y != 0 && q.y > a.q_conf) + (vm.z != 0 && q.z > a.q_conf) +
-          (vm.w != 0 && q.w > a.q_conf);
-    reinterpret_cast<longlong2*>(o_idx + k0)[0] = m01;
-    reinterpret_cast<longlong2*>(o_idx + k0)[1] = m23;
-    *reinterpret_cast<uchar4*>(o_valid + k0) = make_uchar4(vm.x != 0, vm.y != 0, vm.z != 0, vm.w != 0);
-    *reinterpret_cast<float4*>(o_q + k0) = q;
+  for (int sub = 0; sub < a.iters; sub++) {
+  const int wbase = (blockIdx.x * a.iters + sub) * kAdmitChunk + warp * 128;
+  if (wbase >= n) break;
+  if (vec && wbase + 128 <= n) {
+    longlong2 m[2];
+    uchar2 vm[2];
+    float2 qd2[2];
+#pragma unroll
+    for (int hlf = 0; hlf < 2; hlf++) {
+      const int k = wbase + hlf * 64 + 2 * lane;
+      m[hlf] = __ldcs(reinterpret_cast<const longlong2*>(idx + k));
+      vm[hlf] = __ldcs(reinterpret_cast<const uchar2*>(valid + k));
+      qd2[hlf] = __ldcs(reinterpret_cast<const float2*>(qd + k));
+    }
+#pragma unroll
+    for (int hlf = 0; hlf < 2; hlf++) {
+      const int k = wbase + hlf * 64 + 2 * lane;
+      float2 q;
+      q.x = admit_q(qs, m[hlf].x, n, qd2[hlf].x);
+      q.y = admit_q(qs, m[hlf].y, n, qd2[hlf].y);
+      cnt += (vm[hlf].x != 0 && q.x > a.q_conf) + (vm[hlf].y != 0 && q.y > a.q_conf);
+      __stcs(reinterpret_cast<longlong2*>(o_idx + k), m[hlf]);
+      __stcs(reinterpret_cast<uchar2*>(o_valid + k), make_uchar2(vm[hlf].x != 0, vm[hlf].y != 0));
+      __stcs(reinterpret_cast<float2*>(o_q + k), q);
+    }
   } else {
     for (int r = 0; r < kAdmitPerThread; r++) {
-      const int k = k0 + r;
+      const int k = wbase + r * 32 + lane;
       if (k >= n) break;
       const long long m = idx[k];
       const bool vm = valid[k] != 0;
@@ -88,6 +100,7 @@ __global__ void __launch_bounds__(kAdmitThreads) edge_admit_kernel(const AdmitAr
       o_valid[k] = vm ? 1 : 0;
       o_q[k] = q;
     }
+  }
   }
   __shared__ int s_cnt[kAdmitThreads / 32];
   cnt = __reduce_add_sync(0xffffffffu, cnt);
@@ -142,7 +155,10 @@ extern "C" int m3r_edge_admit(const int64_t* idx_i2j, const int64_t* idx_j2i, co
   a.s_idx = store_idx; a.s_valid = store_valid; a.s_q = store_Q;
   a.counts = counts_out;
   a.slot0 = slot0; a.n = num_pts; a.batch = batch; a.q_conf = Q_conf;
-  dim3 grid((num_pts + kAdmitChunk - 1) / kAdmitChunk, 2 * batch);
+  const int chunks = (num_pts + kAdmitChunk - 1) / kAdmitChunk;
+  a.iters = 1;
+  while (a.iters < 4 && (long long)((chunks + 2 * a.iters - 1) / (2 * a.iters)) * 2 * batch >= 8LL * kNumSMs) a.iters *= 2;
+  dim3 grid((chunks + a.iters - 1) / a.iters, 2 * batch);
   edge_admit_kernel<<<grid, kAdmitThreads, 0, s>>>(a);
   M3R_LAUNCH_CHECK();
   return M3R_OK;
