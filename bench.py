@@ -287,9 +287,28 @@ def run_gpu(args):
                         "time-bound by instruction issue / L1 gathers, not HBM (see DESIGN.md, profiles/)"}
 
     # ---- e2e: python drop-in module, pinned host inputs, H2D + D2H inside the timed region --------
-    host = {k: v.cpu().pin_memory() for k, v in inp.items() if k not in ("Twc0",)}
-    host["Twc0"] = inp["Twc0"].cpu().pin_memory()
-    h2d = sum(v.numel() * v.element_size() for v in host.values())
+    # The caller keeps a step's inputs in ONE pinned arena (tensors are 256-byte aligned views, laid out in the order
+    # the ops consume them) and mirrors it on the device, so a group of inputs goes up as one contiguous copy.
+    groups = (("rays", "pts", "p0"), ("D11", "D21"), ("Twc0", "Xs", "Cs", "ii", "jj", "idx", "valid", "Q"))
+    assert sorted(k for g_ in groups for k in g_) == sorted(inp.keys())
+    offs, pos, spans = {}, 0, []
+    for g_ in groups:
+        lo = pos
+        for k_ in g_:
+            offs[k_] = pos
+            pos = (pos + inp[k_].numel() * inp[k_].element_size() + 255) // 256 * 256
+        spans.append((lo, pos))
+    arena_bytes = pos
+
+    def arena_views(arena):
+        return {k_: arena[offs[k_]:offs[k_] + inp[k_].numel() * inp[k_].element_size()].view(inp[k_].dtype).view(inp[k_].shape)
+                for k_ in inp}
+
+    host_arena = torch.empty(arena_bytes, dtype=torch.uint8).pin_memory()
+    host = arena_views(host_arena)
+    for k_, v in inp.items():
+        host[k_].copy_(v)
+    h2d = arena_bytes  # what is copied per step (tensor bytes + < 3 KB of alignment padding)
     out_host = {"idx": torch.empty((1, n, 2), dtype=torch.int64).pin_memory(),
                 "conv": torch.empty((1, n), dtype=torch.bool).pin_memory(),
                 "Twc": torch.empty((N, 8), dtype=torch.float32).pin_memory()}
@@ -299,19 +318,16 @@ def run_gpu(args):
     # descriptors, graph slabs) while the compute stream runs each op as soon as its inputs have landed;
     # results come back on a third stream.  Everything is fenced into the timed events of the compute stream.
     s_up, s_down = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
-    groups = (("rays", "pts", "p0"), ("D11", "D21"), ("Twc0", "Xs", "Cs", "ii", "jj", "idx", "valid", "Q"))
-    assert sorted(k for g_ in groups for k in g_) == sorted(host.keys())
-
-    dv = {k: torch.empty_like(v, device=dev) for k, v in host.items()}  # device staging buffers, allocated once
+    dev_arena = torch.empty(arena_bytes, dtype=torch.uint8, device=dev)  # device staging buffers, allocated once
+    dv = arena_views(dev_arena)
 
     def step_e2e():
         cur = torch.cuda.current_stream(dev)
         s_up.wait_stream(cur)  # nothing starts before the timed region opens
         ready = []
         with torch.cuda.stream(s_up):
-            for g_ in groups:
-                for k_ in g_:
-                    dv[k_].copy_(host[k_], non_blocking=True)
+            for lo_, hi_ in spans:
+                dev_arena[lo_:hi_].copy_(host_arena[lo_:hi_], non_blocking=True)
                 ready.append(s_up.record_event())
         cur.wait_event(ready[0])
         p, conv = ops.iter_proj(dv["rays"], dv["pts"], dv["p0"], MATCH_CFG["max_iter"], MATCH_CFG["lambda_init"],
@@ -341,7 +357,8 @@ def run_gpu(args):
     # enqueued before step i's ops, so the copy engine works while the SMs do (frames arrive as a stream; a
     # frame's inputs do not depend on the previous frame's result).  Every step still uploads all of its
     # inputs and reads back all of its results inside the timed region; K steps are timed as one region.
-    dv2 = (dv, {k: torch.empty_like(v) for k, v in dv.items()})
+    dev_arena2 = (dev_arena, torch.empty_like(dev_arena))
+    dv2 = (dv, arena_views(dev_arena2[1]))
     out2 = (out_host, {k: torch.empty_like(v).pin_memory() for k, v in out_host.items()})
     done = [None, None]
 
@@ -350,9 +367,8 @@ def run_gpu(args):
         if done[slot] is not None:
             s_up.wait_event(done[slot])  # the step that last used this buffer set has finished
         with torch.cuda.stream(s_up):
-            for g_ in groups:
-                for k_ in g_:
-                    dv2[slot][k_].copy_(host[k_], non_blocking=True)
+            for lo_, hi_ in spans:
+                dev_arena2[slot][lo_:hi_].copy_(host_arena[lo_:hi_], non_blocking=True)
                 ready.append(s_up.record_event())
         return ready
 
@@ -410,7 +426,7 @@ def run_gpu(args):
                        "`latency_*` is the same loop without overlap between steps (each step timed alone, L2 flushed)",
            "results_identical_across_buffer_sets": pipe_ok,
            "api": "mast3r_slam_backends.iter_proj / refine_matches / gauss_newton_rays (pybind drop-in), pinned host "
-                  "buffers; H2D on a copy stream in op order, each op waits only for its own inputs, D2H on a third stream"}
+                  "buffers (one arena, three contiguous copies); H2D on a copy stream in op order, each op waits only for its own inputs, D2H on a third stream"}
 
     # ---- matching.match(): torch glue around the two ops vs the fused path, rank 0 numbers ---
     d_raw = synth.make_matching_pair(H, W, seed=1001 + 10 * rank, device=dev)
