@@ -33,6 +33,7 @@
 
 #include <cfloat>
 #include <climits>
+#include <cstdlib>
 #include <mutex>
 
 #include "common.cuh"
@@ -276,7 +277,7 @@ __device__ __forceinline__ void staged_columns(const Desc& q, const unsigned cha
 __global__ void __launch_bounds__(kStThreads, 2)
 refine_staged_kernel(const __half* __restrict__ D11, const __half* __restrict__ D21,
                      const int64_t* __restrict__ p1, int64_t* __restrict__ p1_new, int h, int w,
-                     int tiles_x, int dilation_max) {
+                     int tiles_x, int dilation_max, int reuse_ok) {
   extern __shared__ __align__(128) unsigned char sbox[];
   __shared__ int s_red[kStMaxLevels][8];   // umin, umax, vmin, vmax, sum u, sum v, count
   __shared__ int s_red2[kStMaxLevels][4];  // robust pass: umin, umax, vmin, vmax over inliers
@@ -309,6 +310,10 @@ refine_staged_kernel(const __half* __restrict__ D11, const __half* __restrict__ 
   int ub = u0, vb = v0;
   float best = 0.0f;  // numeric_limits<c10::Half>::min() == Half() == 0
   uint32_t phase = 0;
+  // geometry of the box that is resident in shared memory when the previous level staged its whole window in
+  // one pass (block-uniform): a finer level whose window lies inside it is scored without a refill
+  bool res = false;
+  int res_px0 = 0, res_px1 = -1, res_py0 = 0, res_py1 = -1, res_pitch = 0;
   __syncthreads();
 
   for (int d = dilation_max, lvl = 0; d > 0; d--, lvl++) {
@@ -362,8 +367,29 @@ refine_staged_kernel(const __half* __restrict__ D11, const __half* __restrict__ 
       have_box = false;
       inl = false;
     }
+    // ---- the previous level's box still covers this level's window: no refill ---------------------
+    const bool reuse = reuse_ok && res && have_box && bh > 0 && max(umin - rd, 0) >= res_px0 && min(umax + rd, w - 1) <= res_px1 &&
+                       py0 >= res_py0 && py1 <= res_py1;
+    if (reuse) {
+      const bool interior = u0 - rd >= 0 && u0 + rd < w && v0 - rd >= 0 && v0 + rd < h;
+      const bool fast = __all_sync(0xffffffffu, !inl || interior);
+      if (inl) {
+        const int base = ((v0 - rd - res_py0) * res_pitch + (u0 - rd - res_px0)) * kPxBytes;
+        const int rowstep = d * res_pitch * kPxBytes, colstep = d * kPxBytes;
+        int bc = -1;
+        if (fast)
+          staged_columns<false>(q, sbox, base, rowstep, colstep, 0, kStCnt, u0, v0, rd, d, w, h, best, bc);
+        else
+          staged_columns<true>(q, sbox, base, rowstep, colstep, 0, kStCnt, u0, v0, rd, d, w, h, best, bc);
+        if (bc >= 0) {
+          ub = u0 - rd + (bc >> 3) * d;
+          vb = v0 - rd + (bc & 7) * d;
+        }
+      }
+    } else
     // ---- passes over groups of u-offset columns -------------------------------------------------
     if (have_box && bh > 0) {
+      res = false;
       // Row pitch = width rounded up to 8 px (384 B): a 16-byte chunk of pixel (x, y) then lands in bank
       // group (3x + t) mod 8 whatever y is, so the 8 lanes of an LDS.128 wavefront stay conflict-free
       // when neighbouring queries' centres sit on different rows.
@@ -385,6 +411,10 @@ refine_staged_kernel(const __half* __restrict__ D11, const __half* __restrict__ 
                      img + (static_cast<size_t>(py0 + r) * w + px0) * kPxBytes, rowbytes, bar, pol);
           mbar_wait(bar, phase);
           phase ^= 1u;
+          if (i0 == 0 && c == kStCnt) {  // the whole window of this level is resident now
+            res = true;
+            res_px0 = px0; res_px1 = px1; res_py0 = py0; res_py1 = py1; res_pitch = pitch;
+          }
           const bool interior = u0 - rd >= 0 && u0 + rd < w && v0 - rd >= 0 && v0 + rd < h;
           const bool fast = __all_sync(0xffffffffu, !inl || interior);
           if (inl) {
@@ -523,8 +553,12 @@ extern "C" int m3r_refine_matches_f16(const void* D11, const void* D21, const in
       M3R_CUDA_CHECK(attr_err);
       const int tiles_x = (w + m3r::kTile - 1) / m3r::kTile, tiles_y = (h + m3r::kTile - 1) / m3r::kTile;
       dim3 grid(tiles_x * tiles_y, b);
+      static const int reuse_ok = [] {  // debugging knob: M3R_REFINE_REUSE=0 refills the box at every level
+        const char* e = getenv("M3R_REFINE_REUSE");
+        return (e && e[0] == '0') ? 0 : 1;
+      }();
       m3r::refine_staged_kernel<<<grid, m3r::kStThreads, m3r::kStSmemBytes, st>>>(d11, d21, p1, p1_new, h, w,
-                                                                                 tiles_x, dilation_max);
+                                                                                 tiles_x, dilation_max, reuse_ok);
       M3R_LAUNCH_CHECK();
       return M3R_OK;
     }
