@@ -808,8 +808,15 @@ def cpu_reference_step(inp, steps=1, warmup=0, budget_s=25.0):
     iterations, sized from a calibration pass so one step fits `budget_s`; scaled to whole steps."""
     import numpy as np
     from oracle import oracle as orc
-    cores = os.cpu_count() or 1
-    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    # torchrun exports OMP_NUM_THREADS=1 and torch has initialised the OpenMP runtime by now, so the environment no
+    # longer decides: set the thread count of the runtime the oracle libraries share (libgomp) explicitly
+    os.environ["OMP_NUM_THREADS"] = str(cores)
+    try:
+        import ctypes
+        ctypes.CDLL("libgomp.so.1").omp_set_num_threads(int(cores))
+    except OSError:
+        pass
     impl = "reference" if orc.have_ref_host() else "port"
     rays, pts, p0 = _np(inp["rays"]), _np(inp["pts"]), _np(inp["p0"])
     D11, D21 = _np(inp["D11"]), _np(inp["D21"])
