@@ -20,6 +20,7 @@ CU_SOURCES = ["iter_proj.cu", "refine_matches.cu", "gn_accum.cu", "gn_solve.cu",
 HEADERS = ["common.cuh", "gn_common.cuh", "tma.cuh", "gn_device.cuh"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--expt-relaxed-constexpr"]
+NVCC_FLAGS += os.environ.get("M3R_NVCC_EXTRA", "").split()  # e.g. -DM3R_TRACK_PROF for tools/track_prof.py (then rebuild with force)
 HOST_CXX = "/usr/bin/g++"
 
 

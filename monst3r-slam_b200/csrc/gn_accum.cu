@@ -189,31 +189,51 @@ struct AccumArgs {
 };
 
 // relative pose T_ij = T_i^-1 T_j in fp64 -> fp32 3x4
-__device__ __forceinline__ void edge_xform(const float* __restrict__ Ti, const float* __restrict__ Tj, EdgeXform& X) {
-  const double tix = Ti[0], tiy = Ti[1], tiz = Ti[2];
+// element k of the edge transform: k < 9 -> m[k] = s R(q_i^-1 q_j)[k], k >= 9 -> t[k-9]; fp64 arithmetic.
+// One element per call so that the persistent kernel can spread the 12 elements over 12 warps (the serial
+// version cost ~1 us per iteration on its critical path); with a compile-time k the common terms fold.
+__device__ __forceinline__ float edge_xform_elem(const float* __restrict__ Ti, const float* __restrict__ Tj, int k) {
   const double qix = -(double)Ti[3], qiy = -(double)Ti[4], qiz = -(double)Ti[5], qiw = Ti[6];  // q_i^-1
   const double si_inv = 1.0 / (double)Ti[7];
-  const double qjx = Tj[3], qjy = Tj[4], qjz = Tj[5], qjw = Tj[6];
-  // q = q_i^-1 * q_j
-  const double x = qiw * qjx + qix * qjw + qiy * qjz - qiz * qjy;
-  const double y = qiw * qjy - qix * qjz + qiy * qjw + qiz * qjx;
-  const double z = qiw * qjz + qix * qjy - qiy * qjx + qiz * qjw;
-  const double w = qiw * qjw - qix * qjx - qiy * qjy - qiz * qjz;
-  const double s = si_inv * (double)Tj[7];
-  // R(q) as the linear map of actSO3 (no normalisation, like the reference): I + 2w[q]x + 2[q]x^2
-  double R[9] = {1 - 2 * (y * y + z * z), 2 * (x * y - z * w),     2 * (x * z + y * w),
-                 2 * (x * y + z * w),     1 - 2 * (x * x + z * z), 2 * (y * z - x * w),
-                 2 * (x * z - y * w),     2 * (y * z + x * w),     1 - 2 * (x * x + y * y)};
-#pragma unroll
-  for (int k = 0; k < 9; k++) X.m[k] = (float)(s * R[k]);
+  if (k < 9) {
+    const double qjx = Tj[3], qjy = Tj[4], qjz = Tj[5], qjw = Tj[6];
+    // q = q_i^-1 * q_j
+    const double x = qiw * qjx + qix * qjw + qiy * qjz - qiz * qjy;
+    const double y = qiw * qjy - qix * qjz + qiy * qjw + qiz * qjx;
+    const double z = qiw * qjz + qix * qjy - qiy * qjx + qiz * qjw;
+    const double w = qiw * qjw - qix * qjx - qiy * qjy - qiz * qjz;
+    const double s = si_inv * (double)Tj[7];
+    // R(q) as the linear map of actSO3 (no normalisation, like the reference): I + 2w[q]x + 2[q]x^2
+    double r;
+    switch (k) {
+      case 0: r = 1 - 2 * (y * y + z * z); break;
+      case 1: r = 2 * (x * y - z * w); break;
+      case 2: r = 2 * (x * z + y * w); break;
+      case 3: r = 2 * (x * y + z * w); break;
+      case 4: r = 1 - 2 * (x * x + z * z); break;
+      case 5: r = 2 * (y * z - x * w); break;
+      case 6: r = 2 * (x * z - y * w); break;
+      case 7: r = 2 * (y * z + x * w); break;
+      default: r = 1 - 2 * (x * x + y * y); break;
+    }
+    return (float)(s * r);
+  }
   // t = R(q_i^-1) (t_j - t_i) / s_i
-  const double dx = (double)Tj[0] - tix, dy = (double)Tj[1] - tiy, dz = (double)Tj[2] - tiz;
-  const double Ri[9] = {1 - 2 * (qiy * qiy + qiz * qiz), 2 * (qix * qiy - qiz * qiw),     2 * (qix * qiz + qiy * qiw),
-                        2 * (qix * qiy + qiz * qiw),     1 - 2 * (qix * qix + qiz * qiz), 2 * (qiy * qiz - qix * qiw),
-                        2 * (qix * qiz - qiy * qiw),     2 * (qiy * qiz + qix * qiw),     1 - 2 * (qix * qix + qiy * qiy)};
-  X.t[0] = (float)((Ri[0] * dx + Ri[1] * dy + Ri[2] * dz) * si_inv);
-  X.t[1] = (float)((Ri[3] * dx + Ri[4] * dy + Ri[5] * dz) * si_inv);
-  X.t[2] = (float)((Ri[6] * dx + Ri[7] * dy + Ri[8] * dz) * si_inv);
+  const double dx = (double)Tj[0] - (double)Ti[0], dy = (double)Tj[1] - (double)Ti[1], dz = (double)Tj[2] - (double)Ti[2];
+  double a0, a1, a2;
+  switch (k) {
+    case 9: a0 = 1 - 2 * (qiy * qiy + qiz * qiz); a1 = 2 * (qix * qiy - qiz * qiw); a2 = 2 * (qix * qiz + qiy * qiw); break;
+    case 10: a0 = 2 * (qix * qiy + qiz * qiw); a1 = 1 - 2 * (qix * qix + qiz * qiz); a2 = 2 * (qiy * qiz - qix * qiw); break;
+    default: a0 = 2 * (qix * qiz - qiy * qiw); a1 = 2 * (qiy * qiz + qix * qiw); a2 = 1 - 2 * (qix * qix + qiy * qiy); break;
+  }
+  return (float)((a0 * dx + a1 * dy + a2 * dz) * si_inv);
+}
+
+__device__ __forceinline__ void edge_xform(const float* __restrict__ Ti, const float* __restrict__ Tj, EdgeXform& X) {
+#pragma unroll
+  for (int k = 0; k < 9; k++) X.m[k] = edge_xform_elem(Ti, Tj, k);
+#pragma unroll
+  for (int k = 0; k < 3; k++) X.t[k] = edge_xform_elem(Ti, Tj, 9 + k);
 }
 
 // ---- pose-independent fold + compaction, once per solve -----------------------------------------
@@ -741,7 +761,11 @@ gn_track_kernel(const TrackArgs ta) {
   int nfail = 0;
 
   for (int it = 0; it < ta.max_iter; it++) {
-    if (tid == 0) edge_xform(s_pose + (size_t)i * 8, s_pose + (size_t)j * 8, s_X);
+    if (lane == 0 && warp < 12) {  // one element per warp: no divergence, ~0.1 us instead of ~1 us
+      const float v = edge_xform_elem(s_pose + (size_t)i * 8, s_pose + (size_t)j * 8, warp);
+      if (warp < 9) s_X.m[warp] = v;
+      else s_X.t[warp - 9] = v;
+    }
     __syncthreads();  // s_X (and, first iteration, the gathered Xi)
     TRK(1);  // edge xform
     EdgeXform X;

@@ -307,10 +307,94 @@ struct TrackGraph {      // shared-memory copy of what gn_prepare produced (E <=
   int inc_list[16];
 };
 
+// Two keyframes (dim == 7, the frame-to-keyframe case): warp 0 alone assembles the 7x7 system, factors it, solves
+// and retracts with shuffles — lane r owns row r of H / L, pivots travel by shuffle, the only shared-memory traffic is
+// one transpose of L for the back-substitution.  Same operations in the same order as track_solve7 (except the
+// back-substitution, which subtracts in descending k), but ~1/2 the latency of the single-thread version
+// (~1400 dependent instructions) that used to sit on every iteration's critical path.  Call with threadIdx.x < 32.
+__device__ __forceinline__ void track_solve7_warp(const TrackGraph& g, const double* eb, float* pose, float delta_thresh,
+                                                  double* sm, float* dx_sm, int* flags) {
+  const int lane = threadIdx.x & 31;
+  const int r = lane < 7 ? lane : 0;
+  double a[7] = {0, 0, 0, 0, 0, 0, 0};
+  double y = 0.0;
+  for (int q = g.inc_off[1]; q < g.inc_off[2]; q++) {  // every edge of a two-keyframe graph touches the free pose
+    const int ent = g.inc_list[q];
+    const double* b = eb + (ent >> 1) * kEdgeBlock;
+#pragma unroll
+    for (int c = 0; c < 7; c++) a[c] += b[r * 7 + c];
+    const double bv = b[49 + r];
+    y += (ent & 1) ? bv : -bv;  // g_i = -b_e, g_j = +b_e
+  }
+  bool failed = false;
+  double my_rinv = 1.0;
+#pragma unroll
+  for (int j = 0; j < 7; j++) {
+    double d = __shfl_sync(0xffffffffu, a[j], j);
+    if (!(d > 0.0)) {  // non-SPD => dx = 0 (gn_kernels.cu:147-150)
+      d = 1.0;
+      failed = true;
+    }
+    const double rinv = rsqrt(d);
+    const double l = a[j] * rinv;  // lane j: sqrt(d); lanes > j: L[lane][j]
+    a[j] = l;
+    if (lane == j) my_rinv = rinv;
+#pragma unroll
+    for (int c = j + 1; c < 7; c++) a[c] -= l * __shfl_sync(0xffffffffu, l, c);
+  }
+  // L y = g
+#pragma unroll
+  for (int j = 0; j < 7; j++) {
+    const double yj = __shfl_sync(0xffffffffu, y, j) * __shfl_sync(0xffffffffu, my_rinv, j);
+    if (lane == j) y = yj;
+    if (lane > j) y -= a[j] * yj;
+  }
+  // L^T x = y: lane r needs column r of L, i.e. a[r] of the lanes below it -> one transpose through shared memory
+  if (lane < 7) {
+#pragma unroll
+    for (int c = 0; c < 7; c++) sm[lane * 8 + c] = a[c];
+  }
+  __syncwarp();
+  double col[7];
+#pragma unroll
+  for (int j = 0; j < 7; j++) col[j] = sm[j * 8 + r];  // L[j][r]
+#pragma unroll
+  for (int j = 6; j >= 0; j--) {
+    const double xj = __shfl_sync(0xffffffffu, y, j) * __shfl_sync(0xffffffffu, my_rinv, j);
+    if (lane == j) y = xj;
+    if (lane < j) y -= col[j] * xj;
+  }
+  const float mine = failed ? 0.0f : (float)(-y);
+  float xi[7];
+  double tot = 0.0;
+#pragma unroll
+  for (int c = 0; c < 7; c++) {
+    xi[c] = __shfl_sync(0xffffffffu, mine, c);
+    tot += (double)xi[c] * (double)xi[c];
+  }
+  if (lane == 0) {
+    float T[8];
+#pragma unroll
+    for (int c = 0; c < 7; c++) dx_sm[c] = xi[c];
+#pragma unroll
+    for (int c = 0; c < 8; c++) T[c] = pose[8 + c];
+    sim3_retract(xi, T);
+#pragma unroll
+    for (int c = 0; c < 8; c++) pose[8 + c] = T[c];
+    flags[0] = ((float)sqrt(tot) < delta_thresh) ? 1 : 0;
+    flags[1] = failed ? 1 : 0;
+  }
+}
+
 // returns (in *flags, shared): flags[0] = stop (|dx| < delta_thresh), flags[1] = factorisation failed
 __device__ inline void track_solve(const TrackGraph& g, const double* eb, float* pose, int N, int dim,
                                    float delta_thresh, double* sm, float* dx_sm, int* flags) {
   const int tid = threadIdx.x, nt = blockDim.x;
+  if (dim == 7) {
+    if (tid < 32) track_solve7_warp(g, eb, pose, delta_thresh, sm, dx_sm, flags);
+    __syncthreads();
+    return;
+  }
   const int ld = dim + 1, nfree = N - 1;
   double* H = sm;                     // [dim][ld] lower triangle
   double* x = sm + (size_t)dim * ld;  // rhs / solution
