@@ -887,7 +887,39 @@ gn_track_kernel(const TrackArgs ta) {
       __syncthreads();  // s_flags is rewritten by the next iteration
       continue;
     }
-    // CTA 0 (the solver): fixed-order sum of the cpe partials of each edge
+    // CTA 0 (the solver).  The adjoint rows G_e depend on the poses only: the threads that do not poll compute
+    // them while the partials are still arriving.
+    {
+      const int used = pairs * nslice;
+      const int nfree = kTrackThreads - used - (COST ? 32 : 0);
+      if (tid >= used && tid < used + nfree) {
+        for (int row = tid - used; row < 7 * E; row += nfree) {
+          const int ee = row / 7, m = row % 7;
+          const float* Ti = s_pose + (size_t)s_g.ci[ee] * 8;
+          const double tx = Ti[0], ty = Ti[1], tz = Ti[2], x = Ti[3], y = Ti[4], z = Ti[5], w = Ti[6];
+          const double s_inv = 1.0 / (double)Ti[7];
+          const int mm = m < 3 ? m : m - 3;  // column of R used by this row (selects, no indexed local array)
+          const double c0 = mm == 0 ? 1 - 2 * (y * y + z * z) : mm == 1 ? 2 * (x * y - z * w) : 2 * (x * z + y * w);
+          const double c1 = mm == 0 ? 2 * (x * y + z * w) : mm == 1 ? 1 - 2 * (x * x + z * z) : 2 * (y * z - x * w);
+          const double c2 = mm == 0 ? 2 * (x * z - y * w) : mm == 1 ? 2 * (y * z + x * w) : 1 - 2 * (x * x + y * y);
+          double rowv[7] = {0, 0, 0, 0, 0, 0, 0};
+          if (m < 3) {
+            rowv[0] = s_inv * c0; rowv[1] = s_inv * c1; rowv[2] = s_inv * c2;
+            rowv[3] = s_inv * (ty * c2 - tz * c1);
+            rowv[4] = s_inv * (tz * c0 - tx * c2);
+            rowv[5] = s_inv * (tx * c1 - ty * c0);
+            rowv[6] = s_inv * (tx * c0 + ty * c1 + tz * c2);
+          } else if (m < 6) {
+            rowv[3] = c0; rowv[4] = c1; rowv[5] = c2;
+          } else {
+            rowv[6] = 1.0;
+          }
+#pragma unroll
+          for (int c = 0; c < 7; c++) s_G[ee][m * 7 + c] = rowv[c];
+        }
+      }
+    }
+    // fixed-order sum of the cpe partials of each edge
     if (tid < pairs * nslice) {
       const int pr = tid % pairs, sl = tid / pairs;
       const int ee = pr / kAcc, t = pr % kAcc;
@@ -951,41 +983,16 @@ gn_track_kernel(const TrackArgs ta) {
     }
     __syncthreads();
     TRK(5);  // partial sums
-    // adjoints: A_e = G^T M G, b_e = G^T v (groups of 64 threads, one edge each)
+    // adjoints: A_e = G^T M G, b_e = G^T v (groups of 64 threads, one edge each; G_e = s_G[e] is ready)
     for (int e0 = 0; e0 < E; e0 += kTrackThreads / 64) {
       const int grp = tid >> 6, lt = tid & 63, ee = e0 + grp;
       const bool act = ee < E;
       const double* mv = s_mvE + (act ? ee : 0) * kAcc;
-      if (act && lt < 7) {
-        const int m = lt;
-        const float* Ti = s_pose + (size_t)s_g.ci[ee] * 8;
-        const double tx = Ti[0], ty = Ti[1], tz = Ti[2], x = Ti[3], y = Ti[4], z = Ti[5], w = Ti[6];
-        const double s_inv = 1.0 / (double)Ti[7];
-        const double R[9] = {1 - 2 * (y * y + z * z), 2 * (x * y - z * w),     2 * (x * z + y * w),
-                             2 * (x * y + z * w),     1 - 2 * (x * x + z * z), 2 * (y * z - x * w),
-                             2 * (x * z - y * w),     2 * (y * z + x * w),     1 - 2 * (x * x + y * y)};
-        double row[7] = {0, 0, 0, 0, 0, 0, 0};
-        if (m < 3) {
-          const double c0 = R[0 + m], c1 = R[3 + m], c2 = R[6 + m];
-          row[0] = s_inv * c0; row[1] = s_inv * c1; row[2] = s_inv * c2;
-          row[3] = s_inv * (ty * c2 - tz * c1);
-          row[4] = s_inv * (tz * c0 - tx * c2);
-          row[5] = s_inv * (tx * c1 - ty * c0);
-          row[6] = s_inv * (tx * c0 + ty * c1 + tz * c2);
-        } else if (m < 6) {
-          row[3] = R[0 + (m - 3)]; row[4] = R[3 + (m - 3)]; row[5] = R[6 + (m - 3)];
-        } else {
-          row[6] = 1.0;
-        }
-#pragma unroll
-        for (int c = 0; c < 7; c++) s_G[grp][m * 7 + c] = row[c];
-      }
-      __syncthreads();
       if (act && lt < 49) {
         const int p = lt / 7, c = lt % 7;
         double t = 0.0;
 #pragma unroll
-        for (int q = 0; q < 7; q++) t += ((p <= q) ? mv[tri(p, q)] : mv[tri(q, p)]) * s_G[grp][q * 7 + c];
+        for (int q = 0; q < 7; q++) t += ((p <= q) ? mv[tri(p, q)] : mv[tri(q, p)]) * s_G[ee][q * 7 + c];
         s_TT[grp][lt] = t;
       }
       __syncthreads();
@@ -993,13 +1000,13 @@ gn_track_kernel(const TrackArgs ta) {
         const int r = lt / 7, c = lt % 7;
         double s = 0.0;
 #pragma unroll
-        for (int p = 0; p < 7; p++) s += s_G[grp][p * 7 + r] * s_TT[grp][p * 7 + c];
+        for (int p = 0; p < 7; p++) s += s_G[ee][p * 7 + r] * s_TT[grp][p * 7 + c];
         s_eb[ee * kEdgeBlock + lt] = s;
       } else if (act && lt < 56) {
         const int r = lt - 49;
         double s = 0.0;
 #pragma unroll
-        for (int p = 0; p < 7; p++) s += s_G[grp][p * 7 + r] * mv[28 + p];
+        for (int p = 0; p < 7; p++) s += s_G[ee][p * 7 + r] * mv[28 + p];
         s_eb[ee * kEdgeBlock + lt] = s;
       }
       __syncthreads();
