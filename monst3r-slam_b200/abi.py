@@ -13,7 +13,7 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libm3r_b200.so")
+LIB_PATH = os.path.join(_HERE, os.environ.get("M3R_LIB_DIR", "lib"), "libm3r_b200.so")  # (M3R_LIB_DIR: A/B variant builds)
 
 GN_POINTS, GN_RAYS, GN_CALIB = 0, 1, 2
 MAX_KF_ID = 1 << 20

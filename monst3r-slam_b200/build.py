@@ -13,7 +13,7 @@ import sysconfig
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-LIB = os.path.join(HERE, "lib")
+LIB = os.path.join(HERE, os.environ.get("M3R_LIB_DIR", "lib"))  # M3R_LIB_DIR: side-by-side variant builds for A/B timing
 INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 
 CU_SOURCES = ["iter_proj.cu", "refine_matches.cu", "gn_accum.cu", "gn_solve.cu", "gn_driver.cu", "edge_store.cu", "frame_track.cu"]

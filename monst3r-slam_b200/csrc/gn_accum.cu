@@ -623,13 +623,15 @@ gn_accum_kernel(const AccumArgs a) {
 // gn_accum_kernel (each ~20 us of launch + staging + last-CTA serial tail at 2 x 196 608 points).
 #ifdef M3R_TRACK_PROF
 __device__ unsigned long long g_dbg[1024];
+// phase stamps of iteration 5 in the solver CTA (globaltimer, ns): cheap enough not to disturb the timeline
 #define TRK(slot)                                                     \
   do {                                                                \
-    if (blockIdx.x == 0 && tid == 0) {                                \
-      const long long now_ = clock64();                               \
-      a.ss.ctrl[6 + (slot)] += (int)(now_ - trk_t);                      \
-      trk_t = now_;                                                   \
+    if (blockIdx.x == 0 && tid == 0 && it == 5) {                     \
+      unsigned long long gt_;                                         \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_));         \
+      g_dbg[700 + (slot)] = gt_;                                      \
     }                                                                 \
+    (void)trk_t;                                                      \
   } while (0)
 #else
 #define TRK(slot) do { } while (0)
@@ -667,6 +669,7 @@ gn_track_kernel(const TrackArgs ta) {
   __shared__ double s_TT[kTrackThreads / 64][49];
   __shared__ double s_eb[kTrackMaxEdges * kEdgeBlock];
   __shared__ int s_cnt[64];
+  __shared__ int s_pref[65];  // exclusive prefix of s_cnt: the accumulate loop runs over the CTA's points as one range
   __shared__ TrackGraph s_g;
   __shared__ float s_dx[64];
   __shared__ int s_flags[2];
@@ -682,6 +685,11 @@ gn_track_kernel(const TrackArgs ta) {
   if (a.ctrl[CTRL_DONE]) return;  // uniform over the grid: written before this launch
 #ifdef M3R_TRACK_PROF
   long long trk_t = clock64();
+  if (blockIdx.x == 0 && tid == 0) {
+    unsigned long long gt_;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_));
+    g_dbg[720] = gt_;  // kernel start
+  }
 #endif
 
   // shared-memory layout: per unit u a slab of chunk_pts points: Xj | rec | kloc | Xi
@@ -730,6 +738,14 @@ gn_track_kernel(const TrackArgs ta) {
       bulk_g2s(dst + off_k, a.kloc + (size_t)e * n + p_lo, cnt8 * 2u, bar, pol);
     }
   }
+  if (tid == 0) {
+    int run = 0;
+    for (int u = 0; u < nu; u++) {
+      s_pref[u] = run;
+      run += max(s_cnt[u], 0);
+    }
+    s_pref[nu] = run;
+  }
   mbar_wait(smem_u32(&s_bar), 0);
   // gather the matched points of frame i once (they do not depend on the poses)
   {
@@ -746,7 +762,13 @@ gn_track_kernel(const TrackArgs ta) {
       }
     }
   }
-  TRK(0);  // staging + gather
+#ifdef M3R_TRACK_PROF
+  if (blockIdx.x == 0 && tid == 0) {
+    unsigned long long gt_;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_));
+    g_dbg[721] = gt_;  // staging + gather done
+  }
+#endif
   AccumParams prm = a.prm;
   if (KIND == M3R_GN_CALIB) {
     prm.fx = __ldg(a.K + 0);
@@ -777,17 +799,19 @@ gn_track_kernel(const TrackArgs ta) {
 #pragma unroll
     for (int t = 0; t < kAcc; t++) acc[t] = 0.f;
     float cost = 0.f;
-    for (int u = 0; u < nu; u++) {
-      const int cnt = s_cnt[u];
-      const unsigned char* base = dsm + (size_t)u * slab;
-      const float* sx = reinterpret_cast<const float*>(base);
-      const uint2* srec = reinterpret_cast<const uint2*>(base + off_rec);
-      const uint16_t* sk = reinterpret_cast<const uint16_t*>(base + off_k);
-      const float* sxi = reinterpret_cast<const float*>(base + off_xi);
-      for (int k = tid; k < cnt; k += kTrackThreads) {
-        const uint2 rec = srec[k];
-        const float* xj = sx + (int)sk[k] * 3;
-        const float* xi = sxi + k * 3;
+    // one flat range over the surviving points of all units: ceil(total / 512) rounds instead of one partly filled
+    // last round per unit
+    {
+      const int total = s_pref[nu];
+      int u = 0;
+      for (int f = tid; f < total; f += kTrackThreads) {
+        while (f >= s_pref[u + 1]) u++;
+        const int k = f - s_pref[u];
+        const unsigned char* base = dsm + (size_t)u * slab;
+        const float* sx = reinterpret_cast<const float*>(base);
+        const uint2 rec = reinterpret_cast<const uint2*>(base + off_rec)[k];
+        const float* xj = sx + (int)reinterpret_cast<const uint16_t*>(base + off_k)[k] * 3;
+        const float* xi = reinterpret_cast<const float*>(base + off_xi) + k * 3;
         accum_point<KIND>(acc, X, prm, xj[0], xj[1], xj[2], __uint_as_float(rec.y), (int)rec.x, xi[0], xi[1], xi[2],
                           COST ? &cost : nullptr);
       }
@@ -1035,10 +1059,11 @@ gn_track_kernel(const TrackArgs ta) {
                      : "memory");
       }
 #ifdef M3R_TRACK_PROF
-      if (it == 4 && tid == 0) {
+      if (tid == 0) {
         unsigned long long gt;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt));
-        g_dbg[601] = gt;
+        if (it == 4) g_dbg[601] = gt;
+        g_dbg[730 + (it & 63)] = gt;  // pose of iteration `it` published
       }
 #endif
       for (int t = tid; t < N * 8; t += kTrackThreads) a.ss.Twc[t] = s_pose[t];

@@ -18,7 +18,7 @@ for rep in range(1):
     torch.cuda.synchronize()
     ctrl = ws[:64].view(torch.int32).cpu().tolist()
 names = ["stage+gather", "edge_xform", "accumulate", "cta reduce+store", "grid.sync", "partial sums", "adjoints", "solve+retract"]
-tot = sum(ctrl[6:14])
+tot = sum(ctrl[6:14]) or 1
 for k, nm in enumerate(names):
     print("%-18s %8d cycles  %6.2f us  %5.1f%%" % (nm, ctrl[6 + k], ctrl[6 + k] / 1.965e3, 100.0 * ctrl[6 + k] / tot))
 print("total %.1f us over %d iterations" % (tot / 1.965e3, ctrl[1]))
@@ -27,6 +27,12 @@ import ctypes, numpy as np, statistics
 buf = np.zeros(1024, dtype=np.uint64)
 if hasattr(abi.lib, "m3r_debug_read"):
     abi.lib.m3r_debug_read(buf.ctypes.data_as(ctypes.c_void_p), ctypes.c_size_t(buf.nbytes))
+    st = [int(v) for v in buf[700:708]]
+    print("iteration 5 stamps in CTA 0 (ns after the xform stamp):", [v - st[1] for v in st[1:]],
+          "= xform, accumulate, reduce+store, gather, sums, adjoints, solve")
+    k0 = int(buf[720])
+    print("kernel start -> staged:", int(buf[721]) - k0, "ns; pose published at (ns after kernel start):",
+          [int(v) - k0 for v in buf[730:740]])
     t0 = int(buf[601])
     pub = [int(v) - t0 for v in buf[:148]]
     got = [int(v) - t0 for v in buf[301:448]]
