@@ -136,11 +136,9 @@ extern "C" int m3r_track_frame(float* T_WCf, float* T_CkCf_out, const float* T_W
   prm.pixel_border = p->pixel_border;
   prm.z_eps = p->z_eps;
 
-  M3R_CUDA_CHECK(cudaMemsetAsync(dx_out, 0, sizeof(float) * kPose, s));
-  M3R_CUDA_CHECK(cudaMemsetAsync(info_out, 0, sizeof(int32_t) * 4, s));
   track_init_kernel<<<1, 32, 0, s>>>(T_WCk, T_WCf, Twc2, ii, jj);
   M3R_LAUNCH_CHECK();
-  int rc = launch_gn_prepare(ii, jj, L, P, s);
+  int rc = launch_gn_prepare(ii, jj, L, P, s, dx_out, kPose, info_out);  // also zeroes dx_out / info_out
   if (rc != M3R_OK) return rc;
   rc = launch_gn_pack(nullptr, nullptr, valid, Q, L, P, prm, 0, 1, s);
   if (rc != M3R_OK) return rc;

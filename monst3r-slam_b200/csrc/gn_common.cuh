@@ -149,7 +149,8 @@ struct GnFuse {
 };
 
 // entry points implemented in gn_accum.cu / gn_solve.cu (host launchers)
-int launch_gn_prepare(const int64_t* ii, const int64_t* jj, const GnLayout& L, const GnPtrs& P, cudaStream_t s);
+int launch_gn_prepare(const int64_t* ii, const int64_t* jj, const GnLayout& L, const GnPtrs& P, cudaStream_t s,
+                      float* zero_dx = nullptr, int n_dx = 0, int32_t* zero_info = nullptr);
 int launch_gn_pack(const float* Cs, const int64_t* idx, const uint8_t* valid, const float* Q, const GnLayout& L,
                    const GnPtrs& P, const m3r_gn_params& prm, int e_lo, int e_hi, cudaStream_t s);
 int launch_gn_accumulate(const float* Twc, const float* Xs, const float* K, const GnLayout& L, const GnPtrs& P,

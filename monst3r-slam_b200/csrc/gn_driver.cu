@@ -225,9 +225,7 @@ extern "C" int m3r_gauss_newton(float* Twc, const float* Xs, const float* Cs, co
   GnFuse fuse{};
   fuse.Twc = Twc; fuse.dx_out = dx_out; fuse.info_out = info_out; fuse.delta_thresh = params->delta_thresh;
   fuse.enabled = (L.dim <= kSmallDim) && !(shard && shard->comm) && lo == 0 && hi == num_edges;
-  M3R_CUDA_CHECK(cudaMemsetAsync(dx_out, 0, sizeof(float) * kPose * (size_t)(num_kf - 1), s));
-  if (info_out) M3R_CUDA_CHECK(cudaMemsetAsync(info_out, 0, sizeof(int32_t) * 4, s));
-  rc = launch_gn_prepare(ii, jj, L, P, s);
+  rc = launch_gn_prepare(ii, jj, L, P, s, dx_out, kPose * (num_kf - 1), info_out);  // also zeroes dx_out / info_out
   if (rc != M3R_OK) return rc;
   if (params->max_iter > 0) {
     rc = launch_gn_pack(Cs, idx, valid, Q, L, P, *params, lo, hi, s);

@@ -36,7 +36,8 @@ __global__ void __launch_bounds__(1024)
 gn_prepare_kernel(const int64_t* __restrict__ ii, const int64_t* __restrict__ jj, int E, int N,
                   int* __restrict__ ci, int* __restrict__ cj, unsigned* __restrict__ bitmap,
                   unsigned* __restrict__ prefix, int* __restrict__ inc_off, int* __restrict__ inc_list,
-                  int* __restrict__ order, unsigned* __restrict__ counters, int* __restrict__ ctrl) {
+                  int* __restrict__ order, unsigned* __restrict__ counters, int* __restrict__ ctrl,
+                  float* __restrict__ zero_dx, int n_dx, int32_t* __restrict__ zero_info) {
   // presence bitmap over [id_min, id_max] only: keyframe ids are a few hundred apart at most, so the
   // scan touches a handful of words instead of the whole M3R_MAX_KF_ID range
   const int tid = threadIdx.x, nt = blockDim.x;
@@ -50,6 +51,11 @@ gn_prepare_kernel(const int64_t* __restrict__ ii, const int64_t* __restrict__ jj
   }
   for (int k = tid; k <= E; k += nt) counters[k] = 0u;
   if (tid < CTRL_WORDS) ctrl[tid] = 0;
+  // outputs of the solve that follows start from zero (max_iter == 0, or a solve that never runs): folded in
+  // here instead of two cudaMemsetAsync launches in front of every Gauss-Newton call
+  if (zero_dx)
+    for (int k = tid; k < n_dx; k += nt) zero_dx[k] = 0.f;
+  if (zero_info && tid < 4) zero_info[tid] = 0;
   __syncthreads();
   {
     long long lo = M3R_MAX_KF_ID, hi = -1;
@@ -649,9 +655,10 @@ int g_coop_grid = -1;  // CTAs that can be co-resident for the cooperative varia
 
 }  // namespace
 
-int launch_gn_prepare(const int64_t* ii, const int64_t* jj, const GnLayout& L, const GnPtrs& P, cudaStream_t s) {
+int launch_gn_prepare(const int64_t* ii, const int64_t* jj, const GnLayout& L, const GnPtrs& P, cudaStream_t s,
+                      float* zero_dx, int n_dx, int32_t* zero_info) {
   gn_prepare_kernel<<<1, 1024, 0, s>>>(ii, jj, L.num_edges, L.num_kf, P.ci, P.cj, P.bitmap, P.prefix,
-                                       P.inc_off, P.inc_list, P.order, P.counters, P.ctrl);
+                                       P.inc_off, P.inc_list, P.order, P.counters, P.ctrl, zero_dx, n_dx, zero_info);
   M3R_LAUNCH_CHECK();
   return M3R_OK;
 }
