@@ -156,14 +156,21 @@ refine_gather_kernel(const __half* __restrict__ D11, const __half* __restrict__ 
 }
 
 // ---- staged path ---------------------------------------------------------------------------------
-constexpr int kTile = 16;                     // 16 x 16 queries per CTA
-constexpr int kStThreads = kTile * kTile;     // 256
+#ifndef M3R_TILE_X
+#define M3R_TILE_X 16
+#endif
+// queries per CTA (x: a power of two).  32 x 16 with one 220 KB box per SM stages every level in one pass and was
+// measured within 2 % of 16 x 16 with two CTAs per SM on the benchmark pair (and 5 % slower on perfectly coherent
+// matches), so 16 x 16 stays the default; -DM3R_TILE_X=32 builds the other one.
+constexpr int kTileX = M3R_TILE_X, kTileY = 16;
+constexpr int kStThreads = kTileX * kTileY;
 constexpr int kStRadius = 3, kStCnt = 7;
 constexpr int kStMaxLevels = 8;
-constexpr int kCapPx = 2304;                  // staged pixels per pass: 110 592 B -> 2 CTAs / SM (3 CTAs x 72 KB measured slower: 177 vs 166 us)
+constexpr int kCapPx = kTileX == 16 ? 2304 : 4608;  // staged pixels per pass: 110 592 B -> 2 CTAs / SM (3 CTAs x 72 KB measured slower: 177 vs 166 us)
 constexpr int kStSmemBytes = kCapPx * kPxBytes;
 constexpr int kSane = 1 << 16;                // |centre| beyond this never enters the box statistics
-constexpr int kInlierRad = 12;                // robust pass: centres within +-12 px of the tile mean
+constexpr int kInlierRadX = kTileX / 2 + 4;   // robust pass: centres within +-(half tile + 4) px of the tile mean
+constexpr int kInlierRadY = kTileY / 2 + 4;
 
 // columns [i0, i0+c) of one level for one query, candidates read from the staged box.
 // base/rowstep/colstep are byte offsets into the box; bc receives (i << 3 | j) of a new best.
@@ -274,7 +281,7 @@ __device__ __forceinline__ void staged_columns(const Desc& q, const unsigned cha
   }
 }
 
-__global__ void __launch_bounds__(kStThreads, 2)
+__global__ void __launch_bounds__(kStThreads, kTileX == 16 ? 2 : 1)
 refine_staged_kernel(const __half* __restrict__ D11, const __half* __restrict__ D21,
                      const int64_t* __restrict__ p1, int64_t* __restrict__ p1_new, int h, int w,
                      int tiles_x, int dilation_max, int reuse_ok) {
@@ -286,7 +293,7 @@ refine_staged_kernel(const __half* __restrict__ D11, const __half* __restrict__ 
   const int tid = threadIdx.x;
   const int b = blockIdx.y;
   const int tx = blockIdx.x % tiles_x, ty = blockIdx.x / tiles_x;
-  const int qx = tx * kTile + (tid & (kTile - 1)), qy = ty * kTile + (tid >> 4);
+  const int qx = tx * kTileX + (tid & (kTileX - 1)), qy = ty * kTileY + (tid / kTileX);
   const bool valid = qx < w && qy < h;
   const int n = h * w;
   const size_t qi = static_cast<size_t>(b) * n + (valid ? qy * w + qx : 0);
@@ -346,7 +353,7 @@ refine_staged_kernel(const __half* __restrict__ D11, const __half* __restrict__ 
       if (py1 >= py0 && (umax - umin + 1) * (py1 - py0 + 1) > kCapPx) {
         // robust pass (block-uniform): keep the centres near the mean, the rest gathers from global
         const int mu = s_red[lvl][4] / count, mv = s_red[lvl][5] / count;
-        inl = sane && abs(u0 - mu) <= kInlierRad && abs(v0 - mv) <= kInlierRad;
+        inl = sane && abs(u0 - mu) <= kInlierRadX && abs(v0 - mv) <= kInlierRadY;
         const int mnu = __reduce_min_sync(0xffffffffu, inl ? u0 : INT_MAX);
         const int mxu = __reduce_max_sync(0xffffffffu, inl ? u0 : INT_MIN);
         const int mnv = __reduce_min_sync(0xffffffffu, inl ? v0 : INT_MAX);
@@ -551,7 +558,7 @@ extern "C" int m3r_refine_matches_f16(const void* D11, const void* D21, const in
                                         m3r::kStSmemBytes);
       });
       M3R_CUDA_CHECK(attr_err);
-      const int tiles_x = (w + m3r::kTile - 1) / m3r::kTile, tiles_y = (h + m3r::kTile - 1) / m3r::kTile;
+      const int tiles_x = (w + m3r::kTileX - 1) / m3r::kTileX, tiles_y = (h + m3r::kTileY - 1) / m3r::kTileY;
       dim3 grid(tiles_x * tiles_y, b);
       static const int reuse_ok = [] {  // debugging knob: M3R_REFINE_REUSE=0 refills the box at every level
         const char* e = getenv("M3R_REFINE_REUSE");
