@@ -56,6 +56,67 @@ gn_prepare_kernel(const int64_t* __restrict__ ii, const int64_t* __restrict__ jj
   if (zero_dx)
     for (int k = tid; k < n_dx; k += nt) zero_dx[k] = 0.f;
   if (zero_info && tid < 4) zero_info[tid] = 0;
+  if (2 * E <= 32 && N <= 32) {
+    // Small graphs (tracking: 2 edges): everything in warp 0 with shuffles, no block barrier, no pass through global
+    // memory — same outputs as the general path below (which costs ~10 us of barriers for a two-edge graph).
+    if (tid >= 32) return;
+    __syncwarp();  // the zeroing stores above (lanes < 16 own ctrl) before lane 0 writes ctrl[CTRL_BAD]
+    const unsigned full = 0xffffffffu;
+    const int lane = tid;
+    const bool has = lane < 2 * E;
+    const long long id = has ? (lane < E ? ii[lane] : jj[lane - E]) : -1;
+    const bool ok = has && id >= 0 && id < M3R_MAX_KF_ID;
+    int bad = __any_sync(full, has && !ok) ? 1 : 0;
+    bool first = ok;
+    for (int m = 0; m < 2 * E; m++) {
+      const long long om = __shfl_sync(full, id, m);
+      const bool okm = __shfl_sync(full, (int)ok, m) != 0;
+      if (okm && m < lane && om == id) first = false;
+    }
+    const unsigned firstmask = __ballot_sync(full, first);
+    int c = 0;
+    for (int m = 0; m < 2 * E; m++) {
+      const long long om = __shfl_sync(full, id, m);
+      if (((firstmask >> m) & 1u) && om < id) c++;
+    }
+    if (!ok) c = 0;
+    const bool over = ok && c >= N;
+    if (over) c = 0;
+    bad |= __any_sync(full, over) ? 1 : 0;
+    if (has) (lane < E ? ci : cj)[lane < E ? lane : lane - E] = c;
+    if (lane == 0) ctrl[CTRL_BAD] = bad | ((__popc(firstmask) != N) ? 2 : 0);
+    // per edge (lanes e < E): compact endpoints, launch order by (min, max, e)
+    const int ea = c, eb2 = __shfl_sync(full, c, (lane + E) & 31);
+    const long long key = (long long)min(ea, eb2) * N + max(ea, eb2);
+    int rank = 0;
+    for (int f = 0; f < E; f++) {
+      const long long kf = __shfl_sync(full, key, f);
+      rank += (kf < key) || (kf == key && f < lane);
+    }
+    if (lane < E) order[rank] = lane;
+    // incidence lists per compact pose (lanes c < N)
+    int cnt = 0;
+    for (int e = 0; e < E; e++) {
+      const int a = __shfl_sync(full, ea, e), b = __shfl_sync(full, eb2, e);
+      if (a != b) cnt += (a == lane) + (b == lane);
+    }
+    if (lane >= N) cnt = 0;
+    int incl = cnt;
+    for (int off = 1; off < 32; off <<= 1) {
+      const int v = __shfl_up_sync(full, incl, off);
+      if (lane >= off) incl += v;
+    }
+    if (lane == 0) inc_off[0] = 0;
+    if (lane < N) inc_off[lane + 1] = incl;
+    int o = incl - cnt;
+    for (int e = 0; e < E; e++) {
+      const int a = __shfl_sync(full, ea, e), b = __shfl_sync(full, eb2, e);
+      if (a == b || lane >= N) continue;
+      if (a == lane) inc_list[o++] = (e << 1) | 0;
+      if (b == lane) inc_list[o++] = (e << 1) | 1;
+    }
+    return;
+  }
   __syncthreads();
   {
     long long lo = M3R_MAX_KF_ID, hi = -1;
