@@ -422,7 +422,8 @@ def run_gpu(args):
            "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
            "latency_ms_per_step": lat_ms, "latency_px_per_s": world * N_PX / (lat_ms * 1e-3),
            "pipeline": "2 buffer sets: step i+1's H2D is enqueued before step i's ops; K steps timed as one region "
-                       "(pipeline fill included); every step uploads all its inputs and reads back all its results; "
+                       "(pipeline fill included); every step uploads all its inputs and reads back all its results (no L2 flush "
+                       "inside the region: each step's inputs arrive fresh over PCIe into the other buffer set); "
                        "`latency_*` is the same loop without overlap between steps (each step timed alone, L2 flushed)",
            "results_identical_across_buffer_sets": pipe_ok,
            "api": "mast3r_slam_backends.iter_proj / refine_matches / gauss_newton_rays (pybind drop-in), pinned host "
