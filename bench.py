@@ -285,6 +285,18 @@ def run_gpu(args):
                 "frac": kern[dom]["frac_of_hbm_peak"], "traffic": ncu_traffic(dom), "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs)",
                 "note": "algorithmic bytes / CUDA-event time of the kernel launched alone with a cold L2; "
                         "time-bound by instruction issue / L1 gathers, not HBM (see DESIGN.md, profiles/)"}
+    if dom.startswith("refine"):
+        # the limits that do bind this kernel: bit-exact c10::Half arithmetic needs one HMUL2 and one
+        # HADD2 per two rounded MACs (0.5 warp-inst/clk/SMSP, profiles/r01b_ubench_pipes.log), and every
+        # (query, candidate) pair reads 48 B of descriptors from shared memory (128 B/clk/SM)
+        radius, dil_max, feat = 3, 5, inp["D11"].shape[-1]
+        cand = dil_max * (2 * radius + 1) ** 2
+        sm_hz = 148 * 1965.0e6  # B200 boost clock (clocks.max.sm)
+        fp16_us = N_PX * cand * feat / 32 / (4 * 0.5 * sm_hz) * 1e6
+        lds_us = N_PX * cand * feat * 2 / (128 * sm_hz) * 1e6
+        roofline["pipe_bounds"] = {"fp16x2_issue_floor_us": fp16_us, "shared_memory_floor_us": lds_us,
+                                   "frac_of_fp16x2_floor": fp16_us / (kern[dom]["ms"] * 1e3),
+                                   "note": "the two co-equal binding limits of the bit-exact half-precision scoring"}
 
     # ---- e2e: python drop-in module, pinned host inputs, H2D + D2H inside the timed region --------
     # The caller keeps a step's inputs in ONE pinned arena (tensors are 256-byte aligned views, laid out in the order

@@ -233,68 +233,6 @@ __device__ inline void small_solve(const SmallSolveArgs& a, double* sm, bool wri
   }
 }
 
-// One free pose (frame-to-keyframe tracking): the whole factorisation fits in the registers of one
-// thread and is fully unrolled -- no shared-memory round trips or warp barriers on the dependency
-// chain.  Not inlined: it gets its own register allocation instead of spilling next to the
-// accumulators of the calling kernel.
-static __device__ __noinline__ void track_solve7(const double* H, const double* x, int ld, float* pose, float delta_thresh,
-                                          float* dx_sm, int* flags) {
-  double L[28], y[7];
-#pragma unroll
-  for (int r = 0; r < 7; r++) {
-#pragma unroll
-    for (int c = 0; c <= r; c++) L[r * (r + 1) / 2 + c] = H[r * ld + c];
-    y[r] = x[r];
-  }
-  bool failed = false;
-  double inv[7];
-#pragma unroll
-  for (int j = 0; j < 7; j++) {
-    double d = L[j * (j + 1) / 2 + j];
-#pragma unroll
-    for (int k = 0; k < j; k++) d -= L[j * (j + 1) / 2 + k] * L[j * (j + 1) / 2 + k];
-    if (!(d > 0.0)) {
-      d = 1.0;
-      failed = true;
-    }
-    inv[j] = rsqrt(d);
-#pragma unroll
-    for (int r = j + 1; r < 7; r++) {
-      double v = L[r * (r + 1) / 2 + j];
-#pragma unroll
-      for (int k = 0; k < j; k++) v -= L[r * (r + 1) / 2 + k] * L[j * (j + 1) / 2 + k];
-      L[r * (r + 1) / 2 + j] = v * inv[j];
-    }
-  }
-#pragma unroll
-  for (int j = 0; j < 7; j++) {
-#pragma unroll
-    for (int k = 0; k < j; k++) y[j] -= L[j * (j + 1) / 2 + k] * y[k];
-    y[j] *= inv[j];
-  }
-#pragma unroll
-  for (int j = 6; j >= 0; j--) {
-#pragma unroll
-    for (int k = j + 1; k < 7; k++) y[j] -= L[k * (k + 1) / 2 + j] * y[k];
-    y[j] *= inv[j];
-  }
-  float xi[7], T[8];
-  double tot = 0.0;
-#pragma unroll
-  for (int c = 0; c < 7; c++) {
-    xi[c] = failed ? 0.0f : (float)(-y[c]);
-    dx_sm[c] = xi[c];
-    tot += (double)xi[c] * (double)xi[c];
-  }
-#pragma unroll
-  for (int c = 0; c < 8; c++) T[c] = pose[8 + c];
-  sim3_retract(xi, T);
-#pragma unroll
-  for (int c = 0; c < 8; c++) pose[8 + c] = T[c];
-  flags[0] = ((float)sqrt(tot) < delta_thresh) ? 1 : 0;
-  flags[1] = failed ? 1 : 0;
-}
-
 // ---------------------------------------------------------------------------------------------
 // Solve of the persistent tracking kernel: same mathematics as small_solve, laid out for latency.
 // Everything it reads lives in shared memory (edge blocks, poses, the cached graph structure), the
@@ -309,8 +247,8 @@ struct TrackGraph {      // shared-memory copy of what gn_prepare produced (E <=
 
 // Two keyframes (dim == 7, the frame-to-keyframe case): warp 0 alone assembles the 7x7 system, factors it, solves
 // and retracts with shuffles — lane r owns row r of H / L, pivots travel by shuffle, the only shared-memory traffic is
-// one transpose of L for the back-substitution.  Same operations in the same order as track_solve7 (except the
-// back-substitution, which subtracts in descending k), but ~1/2 the latency of the single-thread version
+// one transpose of L for the back-substitution.  Same operations in the same order as the general path below (except the
+// back-substitution, which subtracts in descending k), but ~1/2 the latency of a single-thread version
 // (~1400 dependent instructions) that used to sit on every iteration's critical path.  Call with threadIdx.x < 32.
 __device__ __forceinline__ void track_solve7_warp(const TrackGraph& g, const double* eb, float* pose, float delta_thresh,
                                                   double* sm, float* dx_sm, int* flags) {
@@ -426,9 +364,7 @@ __device__ inline void track_solve(const TrackGraph& g, const double* eb, float*
     x[t] = gsum;
   }
   __syncthreads();
-  if (dim == 7) {
-    if (tid == 0) track_solve7(H, x, ld, pose, delta_thresh, dx_sm, flags);
-  } else if (tid < 32) {
+  if (tid < 32) {
     const int lane = tid;
     const int r0 = lane, r1 = lane + 32;
     bool failed = false;
