@@ -494,17 +494,20 @@ gn_solve_kernel(const SolveArgs a) {
       const int kn = kb + 1;
         {  // D = A_(kn,kn) - X X^T into sB (L_kk^-1 is no longer needed here)
           const int r = tid >> 4, c = tid & 15;
+          // tile (kn, kn) was last written in the previous step's update: its L2 round trip overlaps the products
+          const double* o = &H[(size_t)(kn * kTile) * ld + kn * kTile];
+          const double o00 = __ldcg(&o[(size_t)r * ld + c]), o01 = __ldcg(&o[(size_t)r * ld + c + 16]);
+          const double o10 = __ldcg(&o[(size_t)(r + 16) * ld + c]), o11 = __ldcg(&o[(size_t)(r + 16) * ld + c + 16]);
           double acc00 = 0, acc01 = 0, acc10 = 0, acc11 = 0;
 #pragma unroll 8
           for (int m = 0; m < kTile; m++) {
             const double a0 = sA[r][m], a1 = sA[r + 16][m], b0 = sA[c][m], b1 = sA[c + 16][m];
             acc00 += a0 * b0; acc01 += a0 * b1; acc10 += a1 * b0; acc11 += a1 * b1;
           }
-          const double* o = &H[(size_t)(kn * kTile) * ld + kn * kTile];
-          const double d00 = __ldcg(&o[(size_t)r * ld + c]) - acc00;
-          const double d01 = __ldcg(&o[(size_t)r * ld + c + 16]) - acc01;
-          const double d10 = __ldcg(&o[(size_t)(r + 16) * ld + c]) - acc10;
-          const double d11 = __ldcg(&o[(size_t)(r + 16) * ld + c + 16]) - acc11;
+          const double d00 = o00 - acc00;
+          const double d01 = o01 - acc01;
+          const double d10 = o10 - acc10;
+          const double d11 = o11 - acc11;
           __syncthreads();
           sB[r][c] = (c <= r) ? d00 : 0.0;
           sB[r][c + 16] = (c + 16 <= r) ? d01 : 0.0;
@@ -543,26 +546,28 @@ gn_solve_kernel(const SolveArgs a) {
       }
       const int I = kb + 1 + i, J = kb + 1 + j;
       __syncthreads();
+      // the destination tile travels with the operands: one exposed L2 round trip per tile instead of two
+      const int r = tid >> 4, c = tid & 15;  // thread -> 2x2 outputs: rows r, r+16 ; cols c, c+16
+      double* o = &H[(size_t)(I * kTile) * ld + J * kTile];
+      const double o00 = __ldcg(&o[(size_t)r * ld + c]), o01 = __ldcg(&o[(size_t)r * ld + c + 16]);
+      const double o10 = __ldcg(&o[(size_t)(r + 16) * ld + c]), o11 = __ldcg(&o[(size_t)(r + 16) * ld + c + 16]);
       for (int t = tid; t < kTile * kTile; t += kSolveThreads) {
-        const int r = t >> 5, c = t & 31;
-        sA[r][c] = __ldcg(&H[(size_t)(I * kTile + r) * ld + kb * kTile + c]);
-        sB[r][c] = __ldcg(&H[(size_t)(J * kTile + r) * ld + kb * kTile + c]);
+        const int rr = t >> 5, cc = t & 31;
+        sA[rr][cc] = __ldcg(&H[(size_t)(I * kTile + rr) * ld + kb * kTile + cc]);
+        sB[rr][cc] = __ldcg(&H[(size_t)(J * kTile + rr) * ld + kb * kTile + cc]);
       }
       __syncthreads();
-      // thread -> 2x2 outputs: rows r, r+16 ; cols c, c+16
       {
-        const int r = tid >> 4, c = tid & 15;
         double acc00 = 0, acc01 = 0, acc10 = 0, acc11 = 0;
 #pragma unroll 8
         for (int m = 0; m < kTile; m++) {
           const double a0 = sA[r][m], a1 = sA[r + 16][m], b0 = sB[c][m], b1 = sB[c + 16][m];
           acc00 += a0 * b0; acc01 += a0 * b1; acc10 += a1 * b0; acc11 += a1 * b1;
         }
-        double* o = &H[(size_t)(I * kTile) * ld + J * kTile];
-        o[(size_t)r * ld + c] = __ldcg(&o[(size_t)r * ld + c]) - acc00;
-        o[(size_t)r * ld + c + 16] = __ldcg(&o[(size_t)r * ld + c + 16]) - acc01;
-        o[(size_t)(r + 16) * ld + c] = __ldcg(&o[(size_t)(r + 16) * ld + c]) - acc10;
-        o[(size_t)(r + 16) * ld + c + 16] = __ldcg(&o[(size_t)(r + 16) * ld + c + 16]) - acc11;
+        o[(size_t)r * ld + c] = o00 - acc00;
+        o[(size_t)r * ld + c + 16] = o01 - acc01;
+        o[(size_t)(r + 16) * ld + c] = o10 - acc10;
+        o[(size_t)(r + 16) * ld + c + 16] = o11 - acc11;
       }
     }
     SLV(3);

@@ -158,25 +158,38 @@ iter_proj_kernel(const float* __restrict__ rays_img, const float* __restrict__ p
 // ---- padded-texel path ------------------------------------------------------------------------------
 // The 36-byte texel of the caller's [b,h,w,9] image is only 4-byte aligned, so every tap costs nine
 // scalar LDG and the kernel above is bound by the load/store queue (ncu: lg_throttle is its top stall).
-// With a workspace the image is first re-packed to 48-byte texels
-//     {ray.x, ray.y, ray.z, gu.x | gu.y, gu.z, gv.x, gv.y | gv.z, -, -, -}
-// (one coalesced pass, 7 MB in / 9.4 MB out at 512x384, L2-resident afterwards) and a tap is then one
-// LDG.128 for the error sample and two more (128 + 64 bit) for the gradients: 4 / 12 load instructions
-// per iteration instead of 12 / 36, same values, same arithmetic, same results.
-constexpr int kPadF4 = 3;  // float4 per padded texel
+// With a workspace the image is first re-packed into three PLANES over all b*h*w texels
+//     A float4 {ray.x, ray.y, ray.z, gu.x}   B float4 {gu.y, gu.z, gv.x, gv.y}   C float {gv.z}
+// (one coalesced pass, 7 MB in / 7 MB out at 512x384, L2-resident afterwards) and a tap is then one
+// LDG.128 for the error sample and LDG.128 + LDG.32 for the gradients: 4 / 12 load instructions per
+// iteration instead of 12 / 36, same values, same arithmetic, same results.  Planes rather than one
+// 48-byte texel: neighbouring lanes sample neighbouring pixels, so a warp's 32 x 16 bytes of one tap are
+// (nearly) contiguous -- 4-5 128-byte lines and 16-17 sectors per request instead of 12 lines / ~22 sectors
+// with the interleaved texel; the L1 spends a wavefront per line touched.
+constexpr int kPadF4 = 3;  // float4 of workspace per texel (A, B, and C's float in the third)
+
+struct TexelPlanes {
+  float4* A;
+  float4* B;
+  float* C;
+};
+__host__ __device__ __forceinline__ TexelPlanes texel_planes(float4* ws, size_t npix) {
+  return TexelPlanes{ws, ws + npix, reinterpret_cast<float*>(ws + 2 * npix)};
+}
 
 // One warp re-packs 32 consecutive texels: 1152 contiguous bytes in (72 coalesced float4 loads), a
-// transpose through shared memory (stride 9 floats: conflict-free), 1536 contiguous bytes out (96 coalesced
-// float4 stores).  `src` must be 16-byte aligned; the last partial group of < 32 texels goes scalar.
+// transpose through shared memory (stride 9 floats: conflict-free), then 512 + 512 + 128 contiguous bytes
+// out, one per plane.  `src` must be 16-byte aligned; the last partial group of < 32 texels goes scalar.
 constexpr int kRepackWarps = 8;
 
 __global__ void __launch_bounds__(kRepackWarps * 32)
 iter_proj_repack_kernel(const float* __restrict__ src, float4* __restrict__ dst, size_t npix) {
   __shared__ __align__(16) float s_in[kRepackWarps][32 * kCh];
-  __shared__ __align__(16) float s_out[kRepackWarps][32 * 12];
   const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
   const size_t g0 = (static_cast<size_t>(blockIdx.x) * kRepackWarps + wp) * 32;  // first texel of this warp
   if (g0 >= npix) return;
+  const TexelPlanes P = texel_planes(dst, npix);
+  float v[kCh];
   if (g0 + 32 <= npix) {
     const float4* in4 = reinterpret_cast<const float4*>(src + g0 * kCh);
     float4* sin4 = reinterpret_cast<float4*>(s_in[wp]);
@@ -184,37 +197,31 @@ iter_proj_repack_kernel(const float* __restrict__ src, float4* __restrict__ dst,
     sin4[lane + 32] = __ldg(in4 + lane + 32);
     if (lane < 8) sin4[lane + 64] = __ldg(in4 + lane + 64);
     __syncwarp();
-    float v[kCh];
 #pragma unroll
     for (int j = 0; j < kCh; j++) v[j] = s_in[wp][lane * kCh + j];
-    float4* so4 = reinterpret_cast<float4*>(s_out[wp]);
-    so4[lane * 3 + 0] = make_float4(v[0], v[1], v[2], v[3]);
-    so4[lane * 3 + 1] = make_float4(v[4], v[5], v[6], v[7]);
-    so4[lane * 3 + 2] = make_float4(v[8], 0.f, 0.f, 0.f);
-    __syncwarp();
-    float4* out4 = dst + g0 * kPadF4;
-    out4[lane] = so4[lane];
-    out4[lane + 32] = so4[lane + 32];
-    out4[lane + 64] = so4[lane + 64];
   } else if (g0 + lane < npix) {
-    const size_t i = g0 + lane;
-    const float* sp = src + i * kCh;
-    float v[kCh];
+    const float* sp = src + (g0 + lane) * kCh;
 #pragma unroll
     for (int j = 0; j < kCh; j++) v[j] = __ldg(sp + j);
-    dst[i * kPadF4 + 0] = make_float4(v[0], v[1], v[2], v[3]);
-    dst[i * kPadF4 + 1] = make_float4(v[4], v[5], v[6], v[7]);
-    dst[i * kPadF4 + 2] = make_float4(v[8], 0.f, 0.f, 0.f);
+  } else {
+    return;
   }
+  const size_t i = g0 + lane;
+  P.A[i] = make_float4(v[0], v[1], v[2], v[3]);
+  P.B[i] = make_float4(v[4], v[5], v[6], v[7]);
+  P.C[i] = v[8];
 }
 
 struct TapsP {
-  const float4* __restrict__ p22;  // (v11, u11) top-left texel; p21 = p22 + 3, p12 = p22 + 3 w, p11 = p12 + 3
-  int row;                         // 3 * w
+  const float4* __restrict__ a22;  // plane A at the top-left texel (v11, u11); (v11, u11+1) = +1, next row = +w
+  const float* __restrict__ c22;   // plane C at the same texel
+  size_t plane;                    // plane B = plane A + plane
+  int row;                         // w
   float w11, w12, w21, w22;
 };
 
-__device__ __forceinline__ TapsP make_taps_p(const float4* __restrict__ img, int w, float u, float v) {
+__device__ __forceinline__ TapsP make_taps_p(const float4* __restrict__ A, const float* __restrict__ C, size_t plane,
+                                             int w, float u, float v) {
   TapsP t;
   const int u11 = static_cast<int>(floorf(u));
   const int v11 = static_cast<int>(floorf(v));
@@ -224,8 +231,11 @@ __device__ __forceinline__ TapsP make_taps_p(const float4* __restrict__ img, int
   t.w12 = (1.0f - du) * dv;
   t.w21 = du * (1.0f - dv);
   t.w22 = (1.0f - du) * (1.0f - dv);
-  t.row = kPadF4 * w;
-  t.p22 = img + (static_cast<size_t>(v11) * w + u11) * kPadF4;
+  t.row = w;
+  t.plane = plane;
+  const size_t i = static_cast<size_t>(v11) * w + u11;
+  t.a22 = A + i;
+  t.c22 = C + i;
   return t;
 }
 
@@ -234,8 +244,8 @@ __device__ __forceinline__ TapsP make_taps_p(const float4* __restrict__ img, int
 // normalised interpolated ray minus target -> err, squared error returned; gu.x (4th lane of the same
 // 16 bytes) comes along for free and is kept for the normal equations of an accepted step
 __device__ __forceinline__ float ray_error_p(const TapsP& t, const float tgt[3], float err[3], float& gux) {
-  const float4 a22 = __ldg(t.p22), a21 = __ldg(t.p22 + kPadF4);
-  const float4 a12 = __ldg(t.p22 + t.row), a11 = __ldg(t.p22 + t.row + kPadF4);
+  const float4 a22 = __ldg(t.a22), a21 = __ldg(t.a22 + 1);
+  const float4 a12 = __ldg(t.a22 + t.row), a11 = __ldg(t.a22 + t.row + 1);
   float r[3];
   r[0] = M3R_TAP(t, a11.x, a12.x, a21.x, a22.x);
   r[1] = M3R_TAP(t, a11.y, a12.y, a21.y, a22.y);
@@ -251,12 +261,11 @@ __device__ __forceinline__ float ray_error_p(const TapsP& t, const float tgt[3],
 }
 
 __device__ __forceinline__ Normal normal_eq_p(const TapsP& t, const float err[3], float gux) {
-  const float4 b22 = __ldg(t.p22 + 1), b21 = __ldg(t.p22 + kPadF4 + 1);
-  const float4 b12 = __ldg(t.p22 + t.row + 1), b11 = __ldg(t.p22 + t.row + kPadF4 + 1);
-  const float c22 = __ldg(reinterpret_cast<const float*>(t.p22 + 2));
-  const float c21 = __ldg(reinterpret_cast<const float*>(t.p22 + kPadF4 + 2));
-  const float c12 = __ldg(reinterpret_cast<const float*>(t.p22 + t.row + 2));
-  const float c11 = __ldg(reinterpret_cast<const float*>(t.p22 + t.row + kPadF4 + 2));
+  const float4* pb = t.a22 + t.plane;
+  const float4 b22 = __ldg(pb), b21 = __ldg(pb + 1);
+  const float4 b12 = __ldg(pb + t.row), b11 = __ldg(pb + t.row + 1);
+  const float c22 = __ldg(t.c22), c21 = __ldg(t.c22 + 1);
+  const float c12 = __ldg(t.c22 + t.row), c11 = __ldg(t.c22 + t.row + 1);
   float gx[3], gy[3];
   gx[0] = gux;
   gx[1] = M3R_TAP(t, b11.x, b12.x, b21.x, b22.x);
@@ -284,7 +293,7 @@ struct IterProjPost {
 
 template <bool POST>
 __global__ void __launch_bounds__(kIterProjThreads)
-iter_proj_padded_kernel(const float4* __restrict__ rays_pad, const float* __restrict__ pts3d_norm,
+iter_proj_padded_kernel(float4* __restrict__ rays_pad, size_t npix_all, const float* __restrict__ pts3d_norm,
                         const float* __restrict__ p_init, float* __restrict__ p_new,
                         uint8_t* __restrict__ converged, int h, int w, int n, int max_iter,
                         float lambda_init, float cost_thresh, IterProjPost post) {
@@ -292,7 +301,9 @@ iter_proj_padded_kernel(const float4* __restrict__ rays_pad, const float* __rest
   const int b = blockIdx.y;
   if (k >= n) return;
   const size_t pix = static_cast<size_t>(b) * n + k;
-  const float4* img = rays_pad + static_cast<size_t>(b) * h * w * kPadF4;
+  const TexelPlanes P = texel_planes(rays_pad, npix_all);
+  const float4* imgA = P.A + static_cast<size_t>(b) * h * w;
+  const float* imgC = P.C + static_cast<size_t>(b) * h * w;
 
   const float2 p0 = __ldg(reinterpret_cast<const float2*>(p_init) + pix);
   float u = clampf(p0.x, 1.0f, static_cast<float>(w - 2));
@@ -305,7 +316,7 @@ iter_proj_padded_kernel(const float4* __restrict__ rays_pad, const float* __rest
   bool conv = false;
   if (max_iter > 0) {
     float err[3], gux;
-    TapsP t = make_taps_p(img, w, u, v);
+    TapsP t = make_taps_p(imgA, imgC, npix_all, w, u, v);
     float cost = ray_error_p(t, tgt, err, gux);
     Normal s = normal_eq_p(t, err, gux);
     for (int it = 0; it < max_iter; it++) {
@@ -317,7 +328,7 @@ iter_proj_padded_kernel(const float4* __restrict__ rays_pad, const float* __rest
       const float u_new = clampf(u + delta_u, 1.0f, static_cast<float>(w - 2));
       const float v_new = clampf(v + delta_v, 1.0f, static_cast<float>(h - 2));
       float err_new[3], gux_new;
-      const TapsP tn = make_taps_p(img, w, u_new, v_new);
+      const TapsP tn = make_taps_p(imgA, imgC, npix_all, w, u_new, v_new);
       const float new_cost = ray_error_p(tn, tgt, err_new, gux_new);
       if (new_cost < cost) {
         u = u_new;
@@ -353,7 +364,7 @@ iter_proj_padded_kernel(const float4* __restrict__ rays_pad, const float* __rest
 // contiguous, the second F.normalize and the arange / lin_to_pixel / float chain (~12 torch kernels that
 // move 4-5x the bytes of iter_proj itself).  A CTA normalises a (32+2) x (8+2) patch of X11 into shared
 // memory (reflect padding at the image border), applies the Scharr-like gradients
-// 1/32 [[-3,0,3],[-10,0,10],[-3,0,3]] and its transpose, and writes the 48-byte texels the LM kernel reads;
+// 1/32 [[-3,0,3],[-10,0,10],[-3,0,3]] and its transpose, and writes the three texel planes the LM kernel reads;
 // the same thread normalises X21[k] and emits p_init[k] for its own pixel index k.
 constexpr int kPrepTW = 32, kPrepTH = 8;
 
@@ -361,8 +372,8 @@ __device__ __forceinline__ int reflect(int i, int n) { return i < 0 ? -i : (i >=
 
 __global__ void __launch_bounds__(kPrepTW * kPrepTH)
 match_prep_kernel(const float* __restrict__ X11, const float* __restrict__ X21, const int64_t* __restrict__ idx_init,
-                  float4* __restrict__ rays_pad, float* __restrict__ pts3d_norm, float* __restrict__ p_init, int h,
-                  int w) {
+                  float4* __restrict__ rays_pad, size_t npix_all, float* __restrict__ pts3d_norm,
+                  float* __restrict__ p_init, int h, int w) {
   __shared__ float s_r[3][kPrepTH + 2][kPrepTW + 2 + 1];
   const int b = blockIdx.z;
   const int x0 = blockIdx.x * kPrepTW, y0 = blockIdx.y * kPrepTH;
@@ -395,9 +406,10 @@ match_prep_kernel(const float* __restrict__ X11, const float* __restrict__ X21, 
   }
   const size_t k = static_cast<size_t>(y) * w + x;
   const size_t pix = static_cast<size_t>(b) * h * w + k;
-  rays_pad[pix * kPadF4 + 0] = make_float4(r[0], r[1], r[2], gx[0]);
-  rays_pad[pix * kPadF4 + 1] = make_float4(gx[1], gx[2], gy[0], gy[1]);
-  rays_pad[pix * kPadF4 + 2] = make_float4(gy[2], 0.f, 0.f, 0.f);
+  const TexelPlanes P = texel_planes(rays_pad, npix_all);
+  P.A[pix] = make_float4(r[0], r[1], r[2], gx[0]);
+  P.B[pix] = make_float4(gx[1], gx[2], gy[0], gy[1]);
+  P.C[pix] = gy[2];
   {
     const float* q = X21 + pix * 3;
     const float a0 = __ldg(q), a1 = __ldg(q + 1), a2 = __ldg(q + 2);
@@ -490,7 +502,7 @@ extern "C" int m3r_iter_proj_ws(const float* rays_img, const float* pts3d_norm, 
   M3R_LAUNCH_CHECK();
   dim3 grid((n + m3r::kIterProjThreads - 1) / m3r::kIterProjThreads, b);
   m3r::iter_proj_padded_kernel<false><<<grid, m3r::kIterProjThreads, 0, st>>>(
-      pad, pts3d_norm, p_init, p_new, converged, h, w, n, max_iter, lambda_init, cost_thresh, m3r::IterProjPost{});
+      pad, npix, pts3d_norm, p_init, p_new, converged, h, w, n, max_iter, lambda_init, cost_thresh, m3r::IterProjPost{});
   M3R_LAUNCH_CHECK();
   return M3R_OK;
 }
@@ -552,14 +564,14 @@ extern "C" int m3r_match_fused(const float* X11, const float* X21, const void* D
   const int n = h * w;
   {
     dim3 grid((w + m3r::kPrepTW - 1) / m3r::kPrepTW, (h + m3r::kPrepTH - 1) / m3r::kPrepTH, b);
-    m3r::match_prep_kernel<<<grid, dim3(m3r::kPrepTW, m3r::kPrepTH), 0, st>>>(X11, X21, idx_init, rays, pts, p0, h, w);
+    m3r::match_prep_kernel<<<grid, dim3(m3r::kPrepTW, m3r::kPrepTH), 0, st>>>(X11, X21, idx_init, rays, n_all, pts, p0, h, w);
     M3R_LAUNCH_CHECK();
   }
   {
     m3r::IterProjPost post{X11, X21, p1, dist_thresh};
     dim3 grid((n + m3r::kIterProjThreads - 1) / m3r::kIterProjThreads, b);
     m3r::iter_proj_padded_kernel<true><<<grid, m3r::kIterProjThreads, 0, st>>>(
-        rays, pts, p0, nullptr, valid_out, h, w, n, max_iter, lambda_init, cost_thresh, post);
+        rays, n_all, pts, p0, nullptr, valid_out, h, w, n, max_iter, lambda_init, cost_thresh, post);
     M3R_LAUNCH_CHECK();
   }
   const int64_t* p_final = p1;
