@@ -187,6 +187,9 @@ iter_proj_repack_kernel(const float* __restrict__ src, float4* __restrict__ dst,
   __shared__ __align__(16) float s_in[kRepackWarps][32 * kCh];
   const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
   const size_t g0 = (static_cast<size_t>(blockIdx.x) * kRepackWarps + wp) * 32;  // first texel of this warp
+  // the LM kernel is launched with programmatic stream serialisation: its CTAs may be scheduled (and read their
+  // targets / initial pixels) as soon as every CTA here is running; they wait for this grid before sampling
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   if (g0 >= npix) return;
   const TexelPlanes P = texel_planes(dst, npix);
   float v[kCh];
@@ -311,6 +314,7 @@ iter_proj_padded_kernel(float4* __restrict__ rays_pad, size_t npix_all, const fl
   float tgt[3];
 #pragma unroll
   for (int j = 0; j < 3; j++) tgt[j] = __ldg(pts3d_norm + pix * 3 + j);
+  asm volatile("griddepcontrol.wait;" ::: "memory");  // planes written by the previous kernel (no-op without PDL)
 
   float lambda = lambda_init;
   bool conv = false;
@@ -500,10 +504,17 @@ extern "C" int m3r_iter_proj_ws(const float* rays_img, const float* pts3d_norm, 
   m3r::iter_proj_repack_kernel<<<static_cast<unsigned>((npix + per_cta - 1) / per_cta), m3r::kRepackWarps * 32, 0, st>>>(
       rays_img, pad, npix);
   M3R_LAUNCH_CHECK();
-  dim3 grid((n + m3r::kIterProjThreads - 1) / m3r::kIterProjThreads, b);
-  m3r::iter_proj_padded_kernel<false><<<grid, m3r::kIterProjThreads, 0, st>>>(
-      pad, npix, pts3d_norm, p_init, p_new, converged, h, w, n, max_iter, lambda_init, cost_thresh, m3r::IterProjPost{});
-  M3R_LAUNCH_CHECK();
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((n + m3r::kIterProjThreads - 1) / m3r::kIterProjThreads, b);
+  cfg.blockDim = dim3(m3r::kIterProjThreads);
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  M3R_CUDA_CHECK(cudaLaunchKernelEx(&cfg, m3r::iter_proj_padded_kernel<false>, pad, npix, pts3d_norm, p_init, p_new,
+                                    converged, h, w, n, max_iter, lambda_init, cost_thresh, m3r::IterProjPost{}));
   return M3R_OK;
 }
 
