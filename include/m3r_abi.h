@@ -59,7 +59,7 @@ int m3r_iter_proj(const float* rays_img, const float* pts3d_norm, const float* p
                   float lambda_init, float cost_thresh, void* stream);
 
 /* Same op with a caller-provided scratch buffer of m3r_iter_proj_workspace_bytes(b,h,w) bytes
- * (16-byte aligned): the ray image is first re-packed to 48-byte texels so that every bilinear tap is
+ * (16-byte aligned): the ray image is first re-packed into float4/float planes (48 bytes of scratch per texel) so that every bilinear tap is
  * a 128-bit load.  Results are identical to m3r_iter_proj; workspace == NULL falls back to it. */
 size_t m3r_iter_proj_workspace_bytes(int b, int h, int w);
 int m3r_iter_proj_ws(const float* rays_img, const float* pts3d_norm, const float* p_init, float* p_new,

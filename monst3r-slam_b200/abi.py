@@ -96,7 +96,7 @@ def _req(t, name, dtype=None):
 
 
 def iter_proj(rays_img_with_grad, pts_3d_norm, p_init, max_iter, lambda_init, cost_thresh, padded=True):
-    """padded=True: m3r_iter_proj_ws (48-byte texels in a scratch buffer); False: the plain kernel."""
+    """padded=True: m3r_iter_proj_ws (texel planes in a scratch buffer); False: the plain kernel."""
     for t, nm in ((rays_img_with_grad, "rays_img_with_grad"), (pts_3d_norm, "pts_3d_norm"), (p_init, "p_init")):
         _req(t, nm, torch.float32)
     b, h, w, c = rays_img_with_grad.shape

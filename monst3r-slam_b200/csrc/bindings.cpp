@@ -203,7 +203,7 @@ std::vector<torch::Tensor> iter_proj(torch::Tensor rays_img_with_grad, torch::Te
   auto opts = p_init.options();
   torch::Tensor p_new = torch::empty({b, n, 2}, opts);
   torch::Tensor converged = torch::empty({b, n}, opts.dtype(torch::kBool));
-  // scratch for the 48-byte texel re-pack (torch's caching allocator: no cudaMalloc in steady state)
+  // scratch for the texel-plane re-pack (torch's caching allocator: no cudaMalloc in steady state)
   const size_t ws_bytes = m3r_iter_proj_workspace_bytes(b, h, w);
   torch::Tensor ws = torch::empty({(int64_t)std::max<size_t>(ws_bytes, 16)}, opts.dtype(torch::kUInt8));
   int rc = m3r_iter_proj_ws(rays_img_with_grad.data_ptr<float>(), pts_3d_norm.data_ptr<float>(),
