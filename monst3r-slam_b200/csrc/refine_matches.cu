@@ -161,12 +161,25 @@ refine_gather_kernel(const __half* __restrict__ D11, const __half* __restrict__ 
 #endif
 // queries per CTA (x: a power of two).  32 x 16 with one 220 KB box per SM stages every level in one pass and was
 // measured within 2 % of 16 x 16 with two CTAs per SM on the benchmark pair (and 5 % slower on perfectly coherent
-// matches), so 16 x 16 stays the default; -DM3R_TILE_X=32 builds the other one.
-constexpr int kTileX = M3R_TILE_X, kTileY = 16;
+// matches), so 16 x 16 stays the default; -DM3R_TILE_X=32 builds the other one.  Tile height, box capacity and
+// CTAs per SM are build parameters too (same-box A/B at 512x384, 16 x 16 / 2304 px / 2 CTAs = 0.161 ms:
+// 16 x 12 -> 0.162, 16 x 10 -> 0.164, 16 x 12 with 1536 px and 3 CTAs -> 0.182, 16 x 8 with 1152 px and 4 CTAs
+// -> 0.191): the finer load balance of smaller tiles is paid back by their larger halo share.
+#ifndef M3R_TILE_Y
+#define M3R_TILE_Y 16
+#endif
+#ifndef M3R_CAP_PX
+#define M3R_CAP_PX (M3R_TILE_X == 16 ? 2304 : 4608)
+#endif
+#ifndef M3R_REFINE_CTAS
+#define M3R_REFINE_CTAS (M3R_TILE_X == 16 ? 2 : 1)
+#endif
+constexpr int kTileX = M3R_TILE_X, kTileY = M3R_TILE_Y;
 constexpr int kStThreads = kTileX * kTileY;
+static_assert(kStThreads % 32 == 0, "whole warps only: the box statistics use full-mask warp reductions");
 constexpr int kStRadius = 3, kStCnt = 7;
 constexpr int kStMaxLevels = 8;
-constexpr int kCapPx = kTileX == 16 ? 2304 : 4608;  // staged pixels per pass: 110 592 B -> 2 CTAs / SM (3 CTAs x 72 KB measured slower: 177 vs 166 us)
+constexpr int kCapPx = M3R_CAP_PX;  // staged pixels per pass: 110 592 B -> 2 CTAs / SM (3 CTAs x 72 KB measured slower: 177 vs 166 us)
 constexpr int kStSmemBytes = kCapPx * kPxBytes;
 constexpr int kSane = 1 << 16;                // |centre| beyond this never enters the box statistics
 constexpr int kInlierRadX = kTileX / 2 + 4;   // robust pass: centres within +-(half tile + 4) px of the tile mean
@@ -281,7 +294,7 @@ __device__ __forceinline__ void staged_columns(const Desc& q, const unsigned cha
   }
 }
 
-__global__ void __launch_bounds__(kStThreads, kTileX == 16 ? 2 : 1)
+__global__ void __launch_bounds__(kStThreads, M3R_REFINE_CTAS)
 refine_staged_kernel(const __half* __restrict__ D11, const __half* __restrict__ D21,
                      const int64_t* __restrict__ p1, int64_t* __restrict__ p1_new, int h, int w,
                      int tiles_x, int dilation_max, int reuse_ok) {

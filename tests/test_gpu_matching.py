@@ -47,7 +47,7 @@ def test_iter_proj_vs_reference_cuda_full_size(backends, ref_backends, synth, b)
 
 
 def test_iter_proj_padded_equals_plain_kernel(abi, synth):
-    """the 48-byte-texel path (m3r_iter_proj_ws) and the plain kernel run the same arithmetic on the same
+    """the texel-plane path (m3r_iter_proj_ws) and the plain kernel run the same arithmetic on the same
     values (only the compiler's FMA contraction may differ): identical pixels and flags, sub-1e-4 px floats;
     identity and previous-frame inits, batch 2, ragged n (scalar tail of the re-pack)"""
     need_gpu()
