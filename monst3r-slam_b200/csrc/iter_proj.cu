@@ -24,7 +24,16 @@
 namespace m3r {
 namespace {
 
-constexpr int kIterProjThreads = 128;
+// CTA size / minimum CTAs per SM of the LM kernel are build parameters (tools/ab_iterproj.py, same box, 512x384:
+// 128 threads at 59 registers = 32 resident warps per SM, 1.3 waves -> 27.6 us with the re-pack; forcing one wave
+// with 48 / 40 registers (20-60 bytes of spills) -> 29.7 / 29.7-31.7 us; 64-thread CTAs -> 27.6 us).
+#ifndef M3R_IP_THREADS
+#define M3R_IP_THREADS 128
+#endif
+#ifndef M3R_IP_MINCTAS
+#define M3R_IP_MINCTAS 1
+#endif
+constexpr int kIterProjThreads = M3R_IP_THREADS;
 constexpr int kCh = 9;
 
 struct Taps {
@@ -295,7 +304,7 @@ struct IterProjPost {
 };
 
 template <bool POST>
-__global__ void __launch_bounds__(kIterProjThreads)
+__global__ void __launch_bounds__(kIterProjThreads, M3R_IP_MINCTAS)
 iter_proj_padded_kernel(float4* __restrict__ rays_pad, size_t npix_all, const float* __restrict__ pts3d_norm,
                         const float* __restrict__ p_init, float* __restrict__ p_new,
                         uint8_t* __restrict__ converged, int h, int w, int n, int max_iter,
