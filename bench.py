@@ -615,7 +615,9 @@ def run_global_opt(args, abi, synth, mdist, dev, rank, world, barrier, max_over_
             "accumulate_plus_amortised_pack_frac_of_hbm_peak": nbytes / ((acc_ms + pack_ms / iters) * 1e-3) / 1e9 / peak,
             "accumulate_streamed_bytes_per_rank": 8 * (hi - lo) * n + 12 * touched * n,
             "solve_and_comm_ms_per_iter": (ms - pack_ms) / iters - acc_ms,
-            "collective": "ncclAllReduce(sum, f64) of the [E2,56] edge blocks, once per iteration" if world > 1 else None,
+            "collective": (("in-place ncclAllGather(f64) of the [E2,56] edge blocks (equal contiguous edge ranges), once per iteration"
+                           if E2 % world == 0 and os.environ.get("M3R_GN_EXCHANGE") != "allreduce" else
+                           "ncclAllReduce(sum, f64) of the zero-padded [E2,56] edge blocks, once per iteration") if world > 1 else None),
             "max_abs_pose_err_vs_gt": gerr,
             "working_set": "13 B/pt/edge slabs (>= 0.6 GB per rank at c3/8) exceed the 126 MB L2; not flushed"}
 

@@ -98,7 +98,10 @@ int m3r_match_fused(const float* X11, const float* X21, const void* D11, const v
  * A rank owns directed edges [edge_lo, edge_hi) of the FULL edge list.  idx/valid/Q passed to
  * the op then hold ONLY those edges' slabs ([edge_hi-edge_lo, n]); ii/jj stay full-length so
  * every rank derives the same compact indices.  `comm` is an ncclComm_t (from m3r_comm_init);
- * once per iteration the per-edge 7x7 blocks + 7-vectors (fp64) are all-reduced (sum). */
+ * once per iteration the per-edge 7x7 blocks + 7-vectors (fp64) are exchanged: in place by ncclAllGather when
+ * every rank owns the same number of edges at rank * count (dist.partition_edges with world | num_edges; all
+ * ranks must use that partition), else zero-padded and all-reduced (sum).  M3R_GN_EXCHANGE=allreduce in the
+ * environment of every rank forces the latter. */
 typedef struct m3r_gn_shard {
   int edge_lo;
   int edge_hi;
@@ -156,7 +159,7 @@ int m3r_gn_pack(const float* Cs, const int64_t* idx, const uint8_t* valid, const
                 void* workspace, size_t workspace_bytes, const m3r_gn_shard* shard, void* stream);
 /* accumulate (after m3r_gn_pack): writes the per-edge fp64 blocks EB[num_edges][56] =
  * {A_e (7x7 row-major), b_e (7)} for edges [edge_lo,edge_hi) and zeros for the others
- * (shard == NULL: all edges); all-reduces them when shard->comm is set. */
+ * (shard == NULL: all edges); exchanges them (see m3r_gn_shard) when shard->comm is set. */
 int m3r_gn_accumulate(const float* Twc, const float* Xs, const float* K, int num_kf, int num_pts,
                       int num_edges, const m3r_gn_params* params, void* workspace,
                       size_t workspace_bytes, const m3r_gn_shard* shard, void* stream);

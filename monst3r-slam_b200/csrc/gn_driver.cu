@@ -2,7 +2,7 @@
 //
 // Replaces the three host loops gauss_newton_{points,rays,calib}_cuda of
 // mast3r_slam/backend/src/gn_kernels.cu (:725-811, :1140-1228, :1546-1638).  One GN iteration is
-//     [memset non-owned edge blocks] -> accumulate -> [ncclAllReduce of the edge blocks] -> solve
+//     accumulate -> [exchange of the edge blocks: in-place ncclAllGather, or memset + ncclAllReduce] -> solve
 // all enqueued on the caller's stream; the stop test lives on the device (ctrl[CTRL_DONE]) and later
 // iterations turn into no-ops, so there is no host synchronisation anywhere in the loop.
 #include <dlfcn.h>
@@ -30,6 +30,8 @@ typedef int (*fn_GetUniqueId)(NcclUniqueId*);
 typedef int (*fn_CommInitRank)(void**, int, NcclUniqueId, int);
 typedef int (*fn_CommDestroy)(void*);
 typedef int (*fn_AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t);
+typedef int (*fn_AllGather)(const void*, void*, size_t, int, void*, cudaStream_t);
+typedef int (*fn_CommQuery)(const void*, int*);
 typedef const char* (*fn_GetErrorString)(int);
 
 struct NcclApi {
@@ -38,6 +40,9 @@ struct NcclApi {
   fn_CommInitRank CommInitRank = nullptr;
   fn_CommDestroy CommDestroy = nullptr;
   fn_AllReduce AllReduce = nullptr;
+  fn_AllGather AllGather = nullptr;   // optional (exchange falls back to the all-reduce without them)
+  fn_CommQuery CommCount = nullptr;
+  fn_CommQuery CommUserRank = nullptr;
   fn_GetErrorString GetErrorString = nullptr;
   bool ok = false;
 };
@@ -56,6 +61,9 @@ NcclApi& nccl() {
     api.CommInitRank = (fn_CommInitRank)dlsym(api.handle, "ncclCommInitRank");
     api.CommDestroy = (fn_CommDestroy)dlsym(api.handle, "ncclCommDestroy");
     api.AllReduce = (fn_AllReduce)dlsym(api.handle, "ncclAllReduce");
+    api.AllGather = (fn_AllGather)dlsym(api.handle, "ncclAllGather");
+    api.CommCount = (fn_CommQuery)dlsym(api.handle, "ncclCommCount");
+    api.CommUserRank = (fn_CommQuery)dlsym(api.handle, "ncclCommUserRank");
     api.GetErrorString = (fn_GetErrorString)dlsym(api.handle, "ncclGetErrorString");
     api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.AllReduce;
   });
@@ -100,10 +108,30 @@ int shard_range(const m3r_gn_shard* shard, int num_edges, int* lo, int* hi) {
   return M3R_OK;
 }
 
+// The exchange of the edge blocks is an all-gather over disjoint slots.  When the edge list is split into EQUAL
+// contiguous ranges in rank order (what dist.partition_edges gives whenever world divides the edge count; every
+// rank then takes this branch) it is done as one in-place ncclAllGather: each rank sends only its own blocks and
+// the two memsets of the foreign slots disappear.  Any other partition: zero the foreign slots and sum-all-reduce
+// (exact, a sum with zeros).  M3R_GN_EXCHANGE=allreduce forces the latter (set it on every rank).
+bool exchange_by_allgather(const m3r_gn_shard* shard, int num_edges, int lo, int hi) {
+  static const bool forced_allreduce = [] {
+    const char* e = getenv("M3R_GN_EXCHANGE");
+    return e && std::strcmp(e, "allreduce") == 0;
+  }();
+  NcclApi& api = nccl();
+  if (forced_allreduce || !shard || !shard->comm || !api.AllGather || !api.CommCount || !api.CommUserRank) return false;
+  int world = 0, rank = -1;
+  if (api.CommCount(shard->comm, &world) != 0 || api.CommUserRank(shard->comm, &rank) != 0) return false;
+  if (world < 1 || num_edges % world != 0) return false;
+  const int cnt = num_edges / world;
+  return lo == rank * cnt && hi == lo + cnt;
+}
+
 int accumulate_step(const float* Twc, const float* Xs, const float* K, const GnLayout& L, const GnPtrs& P,
                     const m3r_gn_params& prm, const m3r_gn_shard* shard, int lo, int hi, const GnFuse& fuse,
                     cudaStream_t s) {
-  if (shard && (lo > 0 || hi < L.num_edges)) {
+  const bool gather = exchange_by_allgather(shard, L.num_edges, lo, hi);
+  if (!gather && shard && (lo > 0 || hi < L.num_edges)) {
     // non-owned slots must be exact zeros so that the sum all-reduce acts as an all-gather
     if (lo > 0) M3R_CUDA_CHECK(cudaMemsetAsync(P.eb, 0, sizeof(double) * kEdgeBlock * (size_t)lo, s));
     if (hi < L.num_edges)
@@ -112,7 +140,11 @@ int accumulate_step(const float* Twc, const float* Xs, const float* K, const GnL
   }
   int rc = launch_gn_accumulate(Twc, Xs, K, L, P, prm, lo, hi, fuse, s);
   if (rc != M3R_OK) return rc;
-  if (shard && shard->comm) {
+  if (gather) {
+    const size_t count = (size_t)(hi - lo) * kEdgeBlock;
+    const int nrc = nccl().AllGather(P.eb + (size_t)lo * kEdgeBlock, P.eb, count, kNcclFloat64, shard->comm, s);
+    if (nrc != 0) return nccl_fail("ncclAllGather", nrc);
+  } else if (shard && shard->comm) {
     rc = m3r_comm_allreduce_f64(shard->comm, P.eb, (size_t)L.num_edges * kEdgeBlock, s);
   }
   return rc;

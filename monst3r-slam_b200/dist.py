@@ -3,8 +3,9 @@
 The keyframe graph is partitioned across ranks BY DIRECTED EDGE: rank r owns a contiguous range of
 the (two-way) edge list and holds only those edges' slabs (idx / valid / Q, 13 B per point per edge,
 96 % of the bytes); Xs / Cs / Twc are replicated.  Once per Gauss-Newton iteration the per-edge
-7x7 + 7 fp64 blocks are all-reduced (sum over zero-padded disjoint slots, so the result is exact and
-bit-identical on every rank) and every rank runs the same deterministic solve + retraction.
+7x7 + 7 fp64 blocks are exchanged (in-place all-gather when `partition_edges` gives equal ranges, else a sum
+all-reduce over zero-padded disjoint slots; exact and bit-identical on every rank either way) and every rank
+runs the same deterministic solve + retraction.
 One process per GPU; torch.distributed is only used to ship the 128-byte NCCL unique id.
 """
 import ctypes as C
