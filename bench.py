@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py — headline benchmark of the B200 geometric backend (contract: see DESIGN.md §Measurement).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--global-opt c3|c4|none]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--global-opt both|c3|c4|none]
 
 One "step" = one frame-to-keyframe tracking pass on synthetic 512x384 data (BASELINE.json configs[1]):
 iter_proj + refine_matches on one pointmap pair (24-d descriptors) and gauss_newton_rays on the
@@ -12,8 +12,10 @@ iter_proj + refine_matches on one pointmap pair (24-d descriptors) and gauss_new
   roofline     dominant kernel of the step vs the measured HBM peak (MEASURED_PEAKS.json)
   cpu_baseline the reference's CPU path (oracle/_ref host build of its matching kernels + the GN
                port) on this box's cores, bounded sample; `--impl reference` times only that
-  global_opt   multi-keyframe GN (config 3: 32 kf / 240 directed edges; c4: 256 kf / 2000 edges),
-               edge-sharded over the N ranks with one NCCL all-reduce of the edge blocks per iteration
+  global_opt   multi-keyframe GN, BOTH graphs by default at every N: `global_opt` = configs[2] (32 kf / 240
+               directed edges, rays), `global_opt_c4` = configs[3] (256 kf / 2000 edges, calib); edge-sharded over
+               the N ranks with one NCCL exchange of the edge blocks per iteration; each leg reports
+               `poses_bit_identical_to_unsharded` (rank 0 repeats the solve as a world-size-1 call)
 At N>1 (torchrun) every rank tracks its own frame (replicas, weak scaling; the path has no exchange
 step for single-frame tracking) and the ranks jointly solve the global-opt graph (strong scaling).
 """
@@ -497,14 +499,19 @@ def run_gpu(args):
                       "torch_glue_ms": t_glue, "fused_ms": t_fused, "torch_glue_px_per_s": N_PX / (t_glue * 1e-3),
                       "fused_px_per_s": N_PX / (t_fused * 1e-3), "fused_launches": 5}
 
-    # ---- global optimisation, edge-sharded -------------------------------------------------------
-    gopt = None
+    # ---- global optimisation, edge-sharded: configs[2] (c3) AND configs[3] (c4) at every N ----------
+    gopt = {}
     if args.global_opt != "none":
-        gopt = run_global_opt(args, abi, synth, mdist, dev, rank, world, barrier, max_over_ranks, peak)
+        comm = mdist.init_comm(rank, world, dev) if world > 1 else None
+        for name in (("c3", "c4") if args.global_opt == "both" else (args.global_opt,)):
+            gopt[name] = run_global_opt(args, name, abi, synth, mdist, dev, rank, world, comm, barrier, max_over_ranks, peak)
+        if comm is not None:
+            torch.cuda.synchronize()
+            abi.comm_destroy(comm)
 
     # ---- factor-graph staging, one GPU ---------------------------------------
     fgraph = None
-    if args.global_opt == "c3" and world == 1:
+    if args.global_opt in ("c3", "both") and world == 1:
         torch.cuda.empty_cache()
         fgraph = run_factor_graph(abi, synth, dev, peak)
 
@@ -528,30 +535,41 @@ def run_gpu(args):
                            "l2": "L2 flushed (512 MB fill) before every timed step and kernel rep",
                            "parallelism": f"replicas x{world}" if world > 1 else "1 GPU"},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * K,
-                "roofline": roofline, "kernels": kern, "cpu_baseline": cpu, "global_opt": gopt,
+                "roofline": roofline, "kernels": kern, "cpu_baseline": cpu, "global_opt": gopt.get("c3"), "global_opt_c4": gopt.get("c4"),
                 "match_pipeline": match_pipeline, "factor_graph": fgraph, "frame_tracker": ftrack}
         emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
-def run_global_opt(args, abi, synth, mdist, dev, rank, world, barrier, max_over_ranks, peak):
+GOPT_CFG = {"c3": dict(N=32, E=120, calib=False, seed=1003, configs_index=2),
+            "c4": dict(N=256, E=1000, calib=True, seed=1004, configs_index=3)}
+
+
+def run_global_opt(args, name, abi, synth, mdist, dev, rank, world, comm, barrier, max_over_ranks, peak):
     """Multi-keyframe gauss_newton_rays (config 3) / gauss_newton_calib (config 4), directed edges
     sharded over the ranks (SURVEY §8e): every rank holds Xs/Cs/Twc and ONLY its own edges' slabs;
-    one NCCL all-reduce of the fp64 edge blocks per iteration; strong scaling (the graph is fixed)."""
+    one NCCL exchange of the fp64 edge blocks per iteration; strong scaling (the graph is fixed).
+    At N > 1 rank 0 also keeps the full slabs and repeats the solve UNSHARDED (world-size-1 call, no
+    communicator): `poses_bit_identical_to_unsharded` compares the two results bit for bit."""
+    import hashlib
     import torch
-    cfg = {"c3": dict(N=32, E=120, calib=False, seed=1003), "c4": dict(N=256, E=1000, calib=True, seed=1004)}[args.global_opt]
+    cfg = GOPT_CFG[name]
     g = synth.make_graph(cfg["N"], cfg["E"], H, W, seed=cfg["seed"], device=dev, calib=cfg["calib"])
     N, n, E2 = cfg["N"], N_PX, 2 * cfg["E"]
     order = mdist.pair_aligned_order(g["ii"], g["jj"])
     ii, jj = g["ii"][order].contiguous(), g["jj"][order].contiguous()
-    lo, hi = mdist.partition_edges(E2, world, rank)
+    parts = mdist.partition_edges(E2, world)
+    lo, hi = parts[rank]
+    exchange = mdist.exchange_for_partition(parts, E2) if args.exchange == "auto" else abi.EXCHANGE_ALLREDUCE
     own = order[lo:hi]
     idx, valid, Q = g["idx"][own].contiguous(), g["valid"][own].contiguous(), g["Q"][own].contiguous()
+    full = None
+    if world > 1 and rank == 0:
+        full = (g["idx"][order].contiguous(), g["valid"][order].contiguous(), g["Q"][order].contiguous())
     del g["idx"], g["valid"], g["Q"]
     torch.cuda.empty_cache()
-    comm = mdist.init_comm(rank, world, dev) if world > 1 else None
-    shard = mdist.make_shard(lo, hi, comm) if world > 1 else None
+    shard = mdist.make_shard(lo, hi, comm, exchange) if world > 1 else None
     iters = 10
     if cfg["calib"]:
         prm = abi.make_params(abi.GN_CALIB, 1.0, 10.0, 0.0, 1.5, iters, 0.0, H, W, -10, 1e-6)
@@ -582,6 +600,16 @@ def run_global_opt(args, abi, synth, mdist, dev, rank, world, barrier, max_over_
         b.synchronize()
         ts.append(a.elapsed_time(b))
     ms = max_over_ranks(statistics.median(ts))
+    info_h = [int(v) for v in info.cpu().tolist()]
+    T_sharded = Twc.clone()
+    # every rank must hold the same poses bit for bit (replicated deterministic solve on identical blocks)
+    sha = hashlib.sha1(T_sharded.cpu().numpy().tobytes()).hexdigest()
+    same_on_all_ranks = True
+    if world > 1:
+        import torch.distributed as dist
+        box = [None] * world
+        dist.all_gather_object(box, sha)
+        same_on_all_ranks = all(b_ == box[0] for b_ in box)
     # accumulate alone (rank-local, no collective) for the roofline of the sharded kernel
     abi.gn_prepare(ii, jj, N, n, ws)
     sh_local = mdist.make_shard(lo, hi, None) if world > 1 else None
@@ -599,26 +627,56 @@ def run_global_opt(args, abi, synth, mdist, dev, rank, world, barrier, max_over_
             ta.append(b.elapsed_time(c))
     acc_ms = max_over_ranks(statistics.median(ta))
     pack_ms = max_over_ranks(statistics.median(tp))
+    # the replicated solve alone (assemble + Cholesky + substitutions + retraction from the blocks in the workspace)
+    Ttmp = g["Twc"].clone()
+    tsv = []
+    for r in range(3 + reps):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        Ttmp.copy_(g["Twc"])
+        abi.gn_prepare(ii, jj, N, n, ws)  # resets the iteration / stop state; the edge blocks stay
+        a.record()
+        abi.lib.m3r_gn_solve_retract(abi._ptr(Ttmp), N, n, E2, abi.C.c_float(0.0), abi._ptr(dx), abi._ptr(info),
+                                     abi._ptr(ws), abi.C.c_size_t(ws.numel()), abi._stream())
+        b.record()
+        b.synchronize()
+        if r >= 3:
+            tsv.append(a.elapsed_time(b))
+    solve_ms = max_over_ranks(statistics.median(tsv))
     touched = int(torch.unique(torch.cat((ii[lo:hi], jj[lo:hi]))).numel())
     nbytes = gn_bytes(hi - lo, touched)
-    gerr = float((Twc - g["Twc_gt"]).abs().max().item())
-    if comm is not None:
+    gerr = float((T_sharded - g["Twc_gt"]).abs().max().item())
+    # unsharded repeat on rank 0 (world-size-1 call on the full slabs): bit-identity of the sharded result
+    identical = True if world == 1 else None
+    if full is not None:
+        del ws
+        torch.cuda.empty_cache()
+        ws1, _ = abi.gn_workspace(N, E2, n, dev)
+        T1 = g["Twc"].clone()
+        abi.gauss_newton(prm, T1, g["Xs"], g["Cs"], K, ii, jj, full[0], full[1], full[2], shard=None, workspace=ws1,
+                         info=info, dx=dx)
         torch.cuda.synchronize()
-        abi.comm_destroy(comm)
-    return {"config": f"configs[{2 if args.global_opt == 'c3' else 3}]: {N} keyframes / {E2} directed edges, 512x384, "
+        identical = bool(torch.equal(T1, T_sharded))
+        del ws1, full
+    barrier()
+    torch.cuda.empty_cache()
+    return {"config": f"configs[{cfg['configs_index']}]: {N} keyframes / {E2} directed edges, 512x384, "
                       f"{'gauss_newton_calib' if cfg['calib'] else 'gauss_newton_rays'} x{iters} iters",
-            "scaling": "strong", "n_gpus": world, "ms_per_solve": ms, "iters": iters,
+            "scaling": "strong", "n_gpus": world, "ms_per_solve": ms, "iters": iters, "info": info_h,
             "gn_edge_iters_per_s": E2 * iters / (ms * 1e-3), "accumulate_ms_per_iter": acc_ms,
             "accumulate_GBps_per_gpu": nbytes / (acc_ms * 1e-3) / 1e9,
             "accumulate_frac_of_hbm_peak": nbytes / (acc_ms * 1e-3) / 1e9 / peak,
+            "accumulate_frac_of_nominal_8TBps": nbytes / (acc_ms * 1e-3) / 1e9 / 8000.0,
+            "whole_op_frac_of_hbm_peak": gn_bytes(E2, N) / (ms / iters * 1e-3) / 1e9 / (peak * world),
             "accumulate_bytes_per_rank": nbytes, "pack_ms_per_solve": pack_ms,
             "accumulate_plus_amortised_pack_frac_of_hbm_peak": nbytes / ((acc_ms + pack_ms / iters) * 1e-3) / 1e9 / peak,
             "accumulate_streamed_bytes_per_rank": 8 * (hi - lo) * n + 12 * touched * n,
+            "solve_alone_ms": solve_ms, "solve_dim": 7 * (N - 1),
             "solve_and_comm_ms_per_iter": (ms - pack_ms) / iters - acc_ms,
             "collective": (("in-place ncclAllGather(f64) of the [E2,56] edge blocks (equal contiguous edge ranges), once per iteration"
-                           if E2 % world == 0 and os.environ.get("M3R_GN_EXCHANGE") != "allreduce" else
+                           if exchange == abi.EXCHANGE_ALLGATHER else
                            "ncclAllReduce(sum, f64) of the zero-padded [E2,56] edge blocks, once per iteration") if world > 1 else None),
-            "max_abs_pose_err_vs_gt": gerr,
+            "poses_bit_identical_to_unsharded": identical, "poses_identical_on_all_ranks": same_on_all_ranks,
+            "poses_sha1": sha, "max_abs_pose_err_vs_gt": gerr,
             "working_set": "13 B/pt/edge slabs (>= 0.6 GB per rank at c3/8) exceed the 126 MB L2; not flushed"}
 
 
@@ -950,7 +1008,9 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--global-opt", default="c3", choices=["c3", "c4", "none"])
+    ap.add_argument("--global-opt", default="both", choices=["both", "c3", "c4", "none"])
+    ap.add_argument("--exchange", default="auto", choices=["auto", "allreduce"],
+                    help="edge-block exchange at N > 1: auto = all-gather when the partition is equal, else all-reduce")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     # stdout carries exactly ONE JSON line: anything a library prints on fd 1 meanwhile (NCCL's version banner,

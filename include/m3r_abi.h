@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define M3R_ABI_VERSION 2
+#define M3R_ABI_VERSION 3
 
 /* status codes */
 #define M3R_OK 0
@@ -98,14 +98,23 @@ int m3r_match_fused(const float* X11, const float* X21, const void* D11, const v
  * A rank owns directed edges [edge_lo, edge_hi) of the FULL edge list.  idx/valid/Q passed to
  * the op then hold ONLY those edges' slabs ([edge_hi-edge_lo, n]); ii/jj stay full-length so
  * every rank derives the same compact indices.  `comm` is an ncclComm_t (from m3r_comm_init);
- * once per iteration the per-edge 7x7 blocks + 7-vectors (fp64) are exchanged: in place by ncclAllGather when
- * every rank owns the same number of edges at rank * count (dist.partition_edges with world | num_edges; all
- * ranks must use that partition), else zero-padded and all-reduced (sum).  M3R_GN_EXCHANGE=allreduce in the
- * environment of every rank forces the latter. */
+ * once per iteration the per-edge 7x7 blocks + 7-vectors (fp64) are exchanged.  HOW is part of the
+ * shard description and must be THE SAME VALUE ON EVERY RANK (it selects the NCCL collective; ranks
+ * that disagree would hang):
+ *   M3R_EXCHANGE_ALLREDUCE  any contiguous partition: foreign slots zeroed, sum all-reduce (a sum with
+ *                           zeros is exact).  The safe default.
+ *   M3R_EXCHANGE_ALLGATHER  in-place ncclAllGather of the own slots (half the bytes, no memsets).  Legal
+ *                           only for the equal partition: world | num_edges and rank r owns
+ *                           [r * num_edges / world, (r + 1) * num_edges / world).  A rank whose range is not
+ *                           that returns M3R_ERR_BAD_ARG before anything is enqueued.
+ * dist.exchange_for_partition() derives the value from the global partition, which every rank knows. */
+#define M3R_EXCHANGE_ALLREDUCE 0
+#define M3R_EXCHANGE_ALLGATHER 1
 typedef struct m3r_gn_shard {
   int edge_lo;
   int edge_hi;
   void* comm;
+  int exchange; /* M3R_EXCHANGE_*; ignored when comm == NULL */
 } m3r_gn_shard;
 
 typedef struct m3r_gn_params {

@@ -43,7 +43,10 @@ class TrackParams(C.Structure):
 
 
 class GnShard(C.Structure):
-    _fields_ = [("edge_lo", C.c_int), ("edge_hi", C.c_int), ("comm", C.c_void_p)]
+    _fields_ = [("edge_lo", C.c_int), ("edge_hi", C.c_int), ("comm", C.c_void_p), ("exchange", C.c_int)]
+
+
+EXCHANGE_ALLREDUCE, EXCHANGE_ALLGATHER = 0, 1
 
 
 def _load():

@@ -13,6 +13,7 @@
 #include <c10/cuda/CUDAGuard.h>
 #include <torch/extension.h>
 
+#include <string>
 #include <vector>
 
 #include "../../include/m3r_abi.h"
@@ -27,6 +28,7 @@ struct DistState {
   void* comm = nullptr;
   bool sharded = false;
   int lo = 0, hi = 0;
+  int exchange = M3R_EXCHANGE_ALLREDUCE;  // same value on every rank (m3r_abi.h: m3r_gn_shard)
   bool sync_checks = true;
   std::vector<int64_t> last_info{0, 0, 0, 0};
 } g_dist;
@@ -97,11 +99,14 @@ std::vector<torch::Tensor> gn_common(int kind, torch::Tensor Twc, torch::Tensor 
   auto opts = Twc.options();
   torch::Tensor dx = torch::zeros({std::max(num_kf - 1, 0), 7}, opts);
   if (num_kf < 2 || E < 1 || n < 1) return {dx};
-  const size_t ws_bytes = m3r_gn_workspace_bytes(num_kf, E, n);
+  // a rank keeps packed records for its own edges only (8 + 2 B per point per edge: GBs at 2000 edges)
+  const size_t ws_bytes = m3r_gn_workspace_bytes_sharded(num_kf, E, n, (int)e_local);
   torch::Tensor ws = torch::empty({(int64_t)ws_bytes}, opts.dtype(torch::kUInt8));
   torch::Tensor info = torch::zeros({4}, opts.dtype(torch::kInt32));
-  m3r_gn_shard shard{lo, hi, g_dist.comm};
-  const bool use_shard = g_dist.sharded || g_dist.comm != nullptr;
+  m3r_gn_shard shard{lo, hi, g_dist.comm, g_dist.exchange};
+  // no shard set -> plain single-GPU call even if a communicator exists (every rank would hold ALL edges: an
+  // exchange would count each block `world` times)
+  const bool use_shard = g_dist.sharded;
   int rc = m3r_gauss_newton(Twc.data_ptr<float>(), Xs.data_ptr<float>(), Cs.data_ptr<float>(), Kp,
                             ii.data_ptr<int64_t>(), jj.data_ptr<int64_t>(), idx_ii2jj.data_ptr<int64_t>(),
                             reinterpret_cast<const uint8_t*>(valid_match.data_ptr<bool>()),
@@ -279,10 +284,14 @@ void shutdown_distributed() {
   g_dist.sharded = false;
 }
 
-void set_edge_shard(int lo, int hi) {
+// exchange: "allreduce" (any contiguous partition) or "allgather" (equal partition only) — the SAME on every rank;
+// derive it from the global partition (dist.exchange_for_partition), never from the rank's own range.
+void set_edge_shard(int lo, int hi, const std::string& exchange) {
+  TORCH_CHECK(exchange == "allreduce" || exchange == "allgather", "exchange must be 'allreduce' or 'allgather'");
   g_dist.sharded = true;
   g_dist.lo = lo;
   g_dist.hi = hi;
+  g_dist.exchange = exchange == "allgather" ? M3R_EXCHANGE_ALLGATHER : M3R_EXCHANGE_ALLREDUCE;
 }
 void clear_edge_shard() { g_dist.sharded = false; }
 void set_sync_checks(bool on) { g_dist.sync_checks = on; }
@@ -348,7 +357,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("nccl_unique_id", &nccl_unique_id);
   m.def("init_distributed", &init_distributed);
   m.def("shutdown_distributed", &shutdown_distributed);
-  m.def("set_edge_shard", &set_edge_shard);
+  m.def("set_edge_shard", &set_edge_shard, py::arg("lo"), py::arg("hi"), py::arg("exchange") = "allreduce");
   m.def("clear_edge_shard", &clear_edge_shard);
   m.def("set_sync_checks", &set_sync_checks);
   m.def("last_info", &last_info);

@@ -8,6 +8,7 @@
 #include <dlfcn.h>
 
 #include <cstring>
+#include <cstdint>
 #include <mutex>
 #include <string>
 
@@ -108,29 +109,36 @@ int shard_range(const m3r_gn_shard* shard, int num_edges, int* lo, int* hi) {
   return M3R_OK;
 }
 
-// The exchange of the edge blocks is an all-gather over disjoint slots.  When the edge list is split into EQUAL
-// contiguous ranges in rank order (what dist.partition_edges gives whenever world divides the edge count; every
-// rank then takes this branch) it is done as one in-place ncclAllGather: each rank sends only its own blocks and
-// the two memsets of the foreign slots disappear.  Any other partition: zero the foreign slots and sum-all-reduce
-// (exact, a sum with zeros).  M3R_GN_EXCHANGE=allreduce forces the latter (set it on every rank).
-bool exchange_by_allgather(const m3r_gn_shard* shard, int num_edges, int lo, int hi) {
-  static const bool forced_allreduce = [] {
-    const char* e = getenv("M3R_GN_EXCHANGE");
-    return e && std::strcmp(e, "allreduce") == 0;
-  }();
+// The exchange of the edge blocks is an all-gather over disjoint slots.  Which collective carries it is part of the
+// shard description (m3r_gn_shard::exchange) and therefore the same on every rank by contract: it is derived from
+// the GLOBAL partition (dist.exchange_for_partition), never from a rank's own range or environment, so ranks cannot
+// end up in different collectives.  ALLGATHER (equal contiguous ranges in rank order): one in-place ncclAllGather,
+// each rank sends only its own blocks and the two memsets of the foreign slots disappear.  ALLREDUCE (any
+// partition): zero the foreign slots and sum-all-reduce (exact, a sum with zeros).
+// -> 1 all-gather, 0 all-reduce, < 0 error (an ALLGATHER request this rank's range does not satisfy)
+int exchange_mode(const m3r_gn_shard* shard, int num_edges, int lo, int hi) {
+  if (!shard || !shard->comm) return 0;
+  if (shard->exchange == M3R_EXCHANGE_ALLREDUCE) return 0;
+  if (shard->exchange != M3R_EXCHANGE_ALLGATHER) return M3R_ERR_BAD_ARG;
   NcclApi& api = nccl();
-  if (forced_allreduce || !shard || !shard->comm || !api.AllGather || !api.CommCount || !api.CommUserRank) return false;
+  if (!api.AllGather || !api.CommCount || !api.CommUserRank) return M3R_ERR_NCCL;
   int world = 0, rank = -1;
-  if (api.CommCount(shard->comm, &world) != 0 || api.CommUserRank(shard->comm, &rank) != 0) return false;
-  if (world < 1 || num_edges % world != 0) return false;
+  if (api.CommCount(shard->comm, &world) != 0 || api.CommUserRank(shard->comm, &rank) != 0) return M3R_ERR_NCCL;
+  if (world < 1 || num_edges % world != 0) return M3R_ERR_BAD_ARG;
   const int cnt = num_edges / world;
-  return lo == rank * cnt && hi == lo + cnt;
+  if (lo != rank * cnt || hi != lo + cnt) return M3R_ERR_BAD_ARG;
+  return 1;
 }
 
 int accumulate_step(const float* Twc, const float* Xs, const float* K, const GnLayout& L, const GnPtrs& P,
                     const m3r_gn_params& prm, const m3r_gn_shard* shard, int lo, int hi, const GnFuse& fuse,
                     cudaStream_t s) {
-  const bool gather = exchange_by_allgather(shard, L.num_edges, lo, hi);
+  const int mode = exchange_mode(shard, L.num_edges, lo, hi);
+  if (mode < 0) {
+    set_last_error_text("m3r_gn_shard: exchange = ALLGATHER needs the equal partition (world | num_edges, rank-ordered ranges)");
+    return mode;
+  }
+  const bool gather = mode == 1;
   if (!gather && shard && (lo > 0 || hi < L.num_edges)) {
     // non-owned slots must be exact zeros so that the sum all-reduce acts as an all-gather
     if (lo > 0) M3R_CUDA_CHECK(cudaMemsetAsync(P.eb, 0, sizeof(double) * kEdgeBlock * (size_t)lo, s));
@@ -251,6 +259,10 @@ extern "C" int m3r_gauss_newton(float* Twc, const float* Xs, const float* Cs, co
   int lo, hi;
   rc = shard_range(shard, num_edges, &lo, &hi);
   if (rc != M3R_OK) return rc;
+  if (exchange_mode(shard, num_edges, lo, hi) < 0) {  // before anything is enqueued
+    set_last_error_text("m3r_gn_shard: exchange = ALLGATHER needs the equal partition (world | num_edges, rank-ordered ranges)");
+    return M3R_ERR_BAD_ARG;
+  }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   GnPtrs P = gn_ptrs(L, workspace);
   // small systems without a collective: solve + retract ride in the accumulate kernel (1 launch / iteration)

@@ -3,8 +3,9 @@
 The keyframe graph is partitioned across ranks BY DIRECTED EDGE: rank r owns a contiguous range of
 the (two-way) edge list and holds only those edges' slabs (idx / valid / Q, 13 B per point per edge,
 96 % of the bytes); Xs / Cs / Twc are replicated.  Once per Gauss-Newton iteration the per-edge
-7x7 + 7 fp64 blocks are exchanged (in-place all-gather when `partition_edges` gives equal ranges, else a sum
-all-reduce over zero-padded disjoint slots; exact and bit-identical on every rank either way) and every rank
+7x7 + 7 fp64 blocks are exchanged (in-place all-gather when the GLOBAL partition has equal ranges — decided by
+`exchange_for_partition`, identically on every rank — else a sum all-reduce over zero-padded disjoint slots; exact
+and bit-identical on every rank either way) and every rank
 runs the same deterministic solve + retraction.
 One process per GPU; torch.distributed is only used to ship the 128-byte NCCL unique id.
 """
@@ -57,6 +58,20 @@ def init_comm(rank, world, device=None, group=None):
     return abi.comm_init(rank, world, uid)
 
 
-def make_shard(lo, hi, comm=None):
+def exchange_for_partition(parts, num_edges):
+    """Which collective carries the per-iteration exchange for the GLOBAL partition `parts` = [(lo, hi)] in rank
+    order.  A pure function of data every rank holds, so all ranks pick the same collective (m3r_abi.h:
+    m3r_gn_shard.exchange).  Equal contiguous ranges covering the list -> in-place all-gather, else all-reduce."""
     from . import abi
-    return abi.GnShard(int(lo), int(hi), comm if comm is not None else C.c_void_p(0))
+    world = len(parts)
+    if world < 1 or num_edges % world != 0:
+        return abi.EXCHANGE_ALLREDUCE
+    cnt = num_edges // world
+    ok = all(int(lo) == r * cnt and int(hi) == (r + 1) * cnt for r, (lo, hi) in enumerate(parts))
+    return abi.EXCHANGE_ALLGATHER if ok else abi.EXCHANGE_ALLREDUCE
+
+
+def make_shard(lo, hi, comm=None, exchange=0):
+    """`exchange` must be the same on every rank: take it from exchange_for_partition(all ranks' ranges)."""
+    from . import abi
+    return abi.GnShard(int(lo), int(hi), comm if comm is not None else C.c_void_p(0), int(exchange))

@@ -1,0 +1,116 @@
+"""Worker of tests/test_gpu_multi.py: one process per GPU under torchrun (NCCL).  Shards a 40-keyframe graph by edge
+through the drop-in module's additive API exactly as INTEGRATION.md §3 shows, and through the C ABI, and checks on
+EVERY rank that the poses are bit-identical to the unsharded single-GPU call.  Prints one JSON line per rank."""
+import importlib
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch
+import torch.distributed as dist
+
+RAYS = (0.003, 10.0, 0.0, 1.5)
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    pkg = importlib.import_module("monst3r-slam_b200")
+    abi = importlib.import_module("monst3r-slam_b200.abi")
+    synth = importlib.import_module("monst3r-slam_b200.synth")
+    mdist = importlib.import_module("monst3r-slam_b200.dist")
+    be = pkg.load_drop_in()
+    out = {"rank": rank, "world": world, "cases": {}}
+
+    g = synth.make_graph_exact(40, 90, 3000, seed=40, noise=1e-3, device=dev)  # dim 273: the multi-CTA solver
+    order = mdist.pair_aligned_order(g["ii"], g["jj"])
+    ii, jj = g["ii"][order].contiguous(), g["jj"][order].contiguous()
+    idx, valid, Q = g["idx"][order].contiguous(), g["valid"][order].contiguous(), g["Q"][order].contiguous()
+    E2 = ii.numel()
+
+    def run_be(lo=None, hi=None, how=None):
+        Twc = g["Twc"].clone()
+        if lo is None:
+            be.clear_edge_shard()
+            sl = slice(0, E2)
+        else:
+            be.set_edge_shard(lo, hi, how)
+            sl = slice(lo, hi)
+        (dx,) = be.gauss_newton_rays(Twc, g["Xs"], g["Cs"], ii, jj, idx[sl].contiguous(), valid[sl].contiguous(),
+                                     Q[sl].contiguous(), *RAYS, 10, 0.0)
+        torch.cuda.synchronize()
+        be.clear_edge_shard()
+        return Twc, dx, list(be.last_info())
+
+    # INTEGRATION.md §3, verbatim
+    uid = [be.nccl_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(uid, src=0)
+    be.init_distributed(rank, world, uid[0])
+
+    T_ref, dx_ref, info_ref = run_be()  # unsharded (a communicator exists but no shard is set: plain local call)
+    out["unsharded_info"] = info_ref
+
+    def record(name, T, dx, info):
+        same = bool(torch.equal(T, T_ref) and torch.equal(dx, dx_ref))
+        box = [None] * world
+        dist.all_gather_object(box, T.cpu().numpy().tobytes())
+        out["cases"][name] = {"bit_identical_to_unsharded": same, "identical_across_ranks": all(b == box[0] for b in box),
+                              "info": info, "max_abs_diff": float((T - T_ref).abs().max())}
+
+    parts = mdist.partition_edges(E2, world)
+    assert E2 % world == 0
+    how = "allgather" if mdist.exchange_for_partition(parts, E2) == abi.EXCHANGE_ALLGATHER else "allreduce"
+    out["auto_exchange"] = how
+    record("pybind_equal_allgather", *run_be(*parts[rank], "allgather"))
+    record("pybind_equal_allreduce", *run_be(*parts[rank], "allreduce"))
+    # uneven contiguous partition (rank 0 gets 7 edges more than an equal share): all-reduce is the only legal exchange
+    cuts = [0] + [min(E2, (r + 1) * (E2 // world) + 7) for r in range(world - 1)] + [E2]
+    uneven = [(cuts[r], cuts[r + 1]) for r in range(world)]
+    assert mdist.exchange_for_partition(uneven, E2) == abi.EXCHANGE_ALLREDUCE
+    record("pybind_uneven_allreduce", *run_be(*uneven[rank], "allreduce"))
+    # asking for the all-gather on a range that is not the equal share must fail BEFORE any collective is enqueued
+    # (every rank asks, every rank fails: nobody is left waiting)
+    try:
+        run_be(*uneven[rank], "allgather")
+        out["cases"]["allgather_on_uneven_rejected"] = False
+    except RuntimeError:
+        be.clear_edge_shard()
+        out["cases"]["allgather_on_uneven_rejected"] = True
+    torch.cuda.synchronize()
+    dist.barrier()
+
+    # the same through the C ABI (ctypes), caller-owned sharded workspace
+    comm = mdist.init_comm(rank, world, dev)
+    prm = abi.make_params(abi.GN_RAYS, *RAYS, 10, 0.0)
+    for name, pr in (("cabi_equal_allgather", parts), ("cabi_uneven_allreduce", uneven)):
+        lo, hi = pr[rank]
+        sh = mdist.make_shard(lo, hi, comm, mdist.exchange_for_partition(pr, E2))
+        ws, _ = abi.gn_workspace(40, E2, 3000, dev, edges_local=hi - lo)
+        Twc = g["Twc"].clone()
+        dx, info = abi.gauss_newton(prm, Twc, g["Xs"], g["Cs"], None, ii, jj, idx[lo:hi].contiguous(),
+                                    valid[lo:hi].contiguous(), Q[lo:hi].contiguous(), shard=sh, workspace=ws)
+        torch.cuda.synchronize()
+        record(name, Twc, dx, [int(v) for v in info.cpu().tolist()])
+    # stand-alone m3r_comm_allreduce_f64
+    buf = torch.arange(1000, dtype=torch.float64, device=dev) * (rank + 1)
+    abi._check(abi.lib.m3r_comm_allreduce_f64(comm, abi._ptr(buf), abi.C.c_size_t(buf.numel()), abi._stream()),
+               "m3r_comm_allreduce_f64")
+    torch.cuda.synchronize()
+    want = torch.arange(1000, dtype=torch.float64, device=dev) * (world * (world + 1) // 2)
+    out["cases"]["comm_allreduce_f64_exact"] = bool(torch.equal(buf, want))
+    abi.comm_destroy(comm)
+    be.shutdown_distributed()
+    dist.barrier()
+    sys.stdout.write("M3R_MULTI " + json.dumps(out) + "\n")
+    sys.stdout.flush()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -111,3 +111,18 @@ def test_partition_and_order_properties():
     o = mdist.pair_aligned_order(ii, jj)
     pairs = [(min(int(ii[k]), int(jj[k])), max(int(ii[k]), int(jj[k]))) for k in o]
     assert pairs == sorted(pairs) and pairs[0] == pairs[1] and pairs[2] == pairs[3]
+
+
+def test_exchange_choice_is_a_function_of_the_global_partition():
+    """ranks must not pick the collective from their own range.  exchange_for_partition sees the whole
+    partition: the mixed case of the advisor (world 4, E 8, ranges (0,2),(2,5),(5,6),(6,8)) is all-reduce for everyone."""
+    import importlib
+    mdist = importlib.import_module("monst3r-slam_b200.dist")
+    abi = importlib.import_module("monst3r-slam_b200.abi")
+    assert mdist.exchange_for_partition(mdist.partition_edges(240, 8), 240) == abi.EXCHANGE_ALLGATHER
+    assert mdist.exchange_for_partition(mdist.partition_edges(2000, 8), 2000) == abi.EXCHANGE_ALLGATHER
+    assert mdist.exchange_for_partition(mdist.partition_edges(14, 4), 14) == abi.EXCHANGE_ALLREDUCE
+    assert mdist.exchange_for_partition([(0, 2), (2, 5), (5, 6), (6, 8)], 8) == abi.EXCHANGE_ALLREDUCE
+    assert mdist.exchange_for_partition([(0, 2), (2, 4), (4, 6), (6, 8)], 8) == abi.EXCHANGE_ALLGATHER
+    sh = mdist.make_shard(2, 4, None, abi.EXCHANGE_ALLGATHER)
+    assert (sh.edge_lo, sh.edge_hi, sh.exchange) == (2, 4, 1)
