@@ -40,6 +40,7 @@ GN_RAYS = dict(sigma_ray=0.003, sigma_dist=10.0, C_thresh=0.0, Q_thresh=1.5, max
 BYTES_ITER_PROJ = 65      # per px   
 BYTES_REFINE = 128        # per px
 METRIC = "matched px/s (tracking step: iter_proj + refine_matches + gauss_newton_rays x10, 512x384)"
+WORKLOAD = ("configs[1]: frame-to-keyframe tracking, 512x384, 24-d desc, matching + gauss_newton_rays N=2/E2=2 x10 iters")
 
 
 def gn_bytes(E_local, N_touched, n=N_PX):
@@ -315,12 +316,14 @@ def run_gpu(args):
         kern[name] = {"ms": ms, "launches_per_step": per_step, "bytes": nbytes,
                       "GBps": (nbytes / (ms * 1e-3) / 1e9) if nbytes else None,
                       "frac_of_hbm_peak": (nbytes / (ms * 1e-3) / 1e9 / peak) if nbytes else None,
+                      "frac_of_nominal_8TBps": (nbytes / (ms * 1e-3) / 1e9 / 8000.0) if nbytes else None,
                       "share_of_step": ms * per_step / ms_per_step}
     abi.gn_prepare(inp["ii"], inp["jj"], N, n, ws)
     abi.gn_pack(prm, inp["Cs"], inp["idx"], inp["valid"], inp["Q"], N, E2, ws)
     dom = max(kern, key=lambda k_: kern[k_]["share_of_step"] if kern[k_]["bytes"] else -1)
     roofline = {"kernel": dom, "bound": "hbm", "achieved": kern[dom]["GBps"], "peak": peak, "unit": "GB/s",
-                "frac": kern[dom]["frac_of_hbm_peak"], "traffic": ncu_traffic(dom), "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs)",
+                "frac": kern[dom]["frac_of_hbm_peak"], "frac_of_nominal_8TBps": kern[dom]["frac_of_nominal_8TBps"],
+                "traffic": ncu_traffic(dom), "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs)",
                 "note": "algorithmic bytes / CUDA-event time of the kernel launched alone with a cold L2; "
                         "time-bound by instruction issue / L1 gathers, not HBM (see DESIGN.md, profiles/)"}
     if dom.startswith("refine"):
@@ -530,8 +533,7 @@ def run_gpu(args):
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f32 (iter_proj, GN accumulate) / f16 (refine_matches) / f64 (assemble + Cholesky)",
                 "data": "synthetic",
-                "config": {"workload": "configs[1]: frame-to-keyframe tracking, 512x384, 24-d desc, matching + "
-                                       "gauss_newton_rays N=2/E2=2 x10 iters; one replica per GPU",
+                "config": {"workload": WORKLOAD, "arm": "B200 kernels, one replica per GPU",
                            "l2": "L2 flushed (512 MB fill) before every timed step and kernel rep",
                            "parallelism": f"replicas x{world}" if world > 1 else "1 GPU"},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * K,
@@ -970,10 +972,13 @@ def cpu_reference_step(inp, steps=1, warmup=0, budget_s=25.0):
                      "gauss_newton_rays_s": tg * GN_RAYS["max_iter"] / it_s}
     step_s = statistics.median(est)
     return {"value": N_PX / step_s, "unit": "px/s", "cores": cores,
+            # the GN port parallelises over directed edges like the reference's one-block-per-edge grid: E2 = 2 here
+            "gn_threads_used": min(cores, int(gn[3].shape[0])), "matching_threads_used": cores,
             "kind": "reference" if impl == "reference" else "port",
             "sample": f"{n_s} of {N_PX} query px through the reference's matching kernels built for the host "
                       f"({impl}) + {it_s} of {GN_RAYS['max_iter']} GN iterations (N=2, E2=2, all {N_PX} points) "
-                      f"through the host port of ray_align_kernel + fp64 LLT; scaled to one whole step",
+                      f"through the host port of ray_align_kernel + fp64 LLT (edge-parallel: 2 edges -> 2 of the {cores} threads busy in that leg); "
+                      f"scaled to one whole step",
             "s_per_step": step_s, "parts_s_per_step": parts}
 
 
@@ -984,7 +989,9 @@ def run_reference(args):
     if rank != 0:
         return
     import torch
-    _, _, synth, matching, _ = load_pkg()  # synth + torch glue only: no kernel of ours is on this path
+    # synth + torch glue ONLY: the reference arm must not map libm3r_b200.so (abi / dist / the drop-in stay unimported)
+    synth = importlib.import_module("monst3r-slam_b200.synth")
+    matching = importlib.import_module("monst3r-slam_b200.matching")
     inp = make_tracking_inputs(synth, matching, torch.device("cpu"), 1001)
     K, Wm = args.steps, args.warmup
     budget = max(4.0, min(25.0, 150.0 / max(1, K + Wm)))
@@ -993,8 +1000,7 @@ def run_reference(args):
             "steps": K, "warmup": Wm, "ms_per_step": cpu["s_per_step"] * 1e3, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None,
             "dtype": "f32 / f16 (c10::Half on host) / f64 solve", "data": "synthetic",
-            "config": {"workload": "configs[1]: frame-to-keyframe tracking, 512x384, 24-d desc, matching + "
-                                   "gauss_newton_rays N=2/E2=2 x10 iters; reference CPU path, rank 0 only",
+            "config": {"workload": WORKLOAD, "arm": "reference CPU path, rank 0 only",
                        "parallelism": f"host cores x{cpu['cores']} (OpenMP)"},
             "cpu_baseline": cpu,
             "e2e": {"value": cpu["value"], "unit": "px/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
