@@ -102,6 +102,13 @@ class KeyframeBuffer:
         self.T_WC.index_copy_(0, idx, T_WCs)
 
 
+class _PoseData:
+    """what SharedKeyframes.update_T_WCs reads of a lietorch.Sim3: `.data` [k,1,8]"""
+
+    def __init__(self, data):
+        self.data = data
+
+
 class FactorGraph:
     """global_opt.py:12-215 with the model call factored out: `add_factors` takes a `match_fn(ii, jj)`
     returning the eight tensors of mast3r_match_symmetric; `add_factors_from_matches` takes them directly."""
@@ -122,21 +129,29 @@ class FactorGraph:
         self._unique = None
 
     # -- views with the reference's attribute names (global_opt.py:17-25), zero-copy, strided over the pairs
-    def _dir(self, t, d):
-        return t[d:2 * self.num_edges:2] if self.store is not None else None
+    _EMPTY = {"ii2": (torch.int64, ()), "jj2": (torch.int64, ()), "idx": (torch.int64, (0,)), "valid": (torch.bool, (0,)),
+              "Q": (torch.float32, (0,))}
+
+    def _dir(self, name, d):
+        """direction d (0: i->j, 1: j->i) of slab `name`; before the first add_factors the reference's attributes are
+        EMPTY tensors (global_opt.py:17-25), so are these"""
+        if self.store is None:
+            dt, tail = self._EMPTY[name]
+            return torch.empty((0,) + tail, dtype=dt, device=self.device)
+        return getattr(self.store, name)[d:2 * self.num_edges:2]
 
     @property
     def num_edges(self):
         return self.store.num_und if self.store is not None else 0
 
-    ii = property(lambda self: self._dir(self.store.ii2, 0))
-    jj = property(lambda self: self._dir(self.store.jj2, 0))
-    idx_ii2jj = property(lambda self: self._dir(self.store.idx, 0))
-    idx_jj2ii = property(lambda self: self._dir(self.store.idx, 1))
-    valid_match_j = property(lambda self: self._dir(self.store.valid, 0).unsqueeze(-1))
-    valid_match_i = property(lambda self: self._dir(self.store.valid, 1).unsqueeze(-1))
-    Q_ii2jj = property(lambda self: self._dir(self.store.Q, 0).unsqueeze(-1))
-    Q_jj2ii = property(lambda self: self._dir(self.store.Q, 1).unsqueeze(-1))
+    ii = property(lambda self: self._dir("ii2", 0))
+    jj = property(lambda self: self._dir("jj2", 0))
+    idx_ii2jj = property(lambda self: self._dir("idx", 0))
+    idx_jj2ii = property(lambda self: self._dir("idx", 1))
+    valid_match_j = property(lambda self: self._dir("valid", 0).unsqueeze(-1))
+    valid_match_i = property(lambda self: self._dir("valid", 1).unsqueeze(-1))
+    Q_ii2jj = property(lambda self: self._dir("Q", 0).unsqueeze(-1))
+    Q_jj2ii = property(lambda self: self._dir("Q", 1).unsqueeze(-1))
 
     def add_factors(self, ii, jj, min_match_frac, is_reloc=False):
         """global_opt.py:31-99; the symmetric matcher (:40-52) is the injected match_fn"""
@@ -213,8 +228,14 @@ class FactorGraph:
 
     def _finish(self, T_WCs, unique_kf_idx, in_place):
         pin = self.cfg["pin"]
-        if not in_place and hasattr(self.frames, "update_T_WCs"):
+        if in_place or not hasattr(self.frames, "update_T_WCs"):
+            return
+        if isinstance(self.frames, KeyframeBuffer):
             self.frames.update_T_WCs(T_WCs[pin:], unique_kf_idx[pin:])  # :152, :213
+        else:
+            # the reference's SharedKeyframes (frame.py:362-364) does `self.T_WC[idx] = T_WCs.data` on a [buffer,1,8]
+            # tensor with a lietorch.Sim3 whose .data is [k,1,8]: hand it the same shape behind the same attribute
+            self.frames.update_T_WCs(_PoseData(T_WCs[pin:].reshape(-1, 1, 8)), unique_kf_idx[pin:])
 
     def solve_GN_rays(self):
         """:121-153"""

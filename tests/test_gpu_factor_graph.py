@@ -249,3 +249,57 @@ def test_is_reloc_rejection_commits_nothing(fgm):
     # not a relocalisation: the bad pairs are dropped, the call reports that nothing was added
     assert fg.add_factors_from_matches([0, 1], [3, 4], tuple(t.cuda() for t in bad), 0.1) is False
     assert fg.num_edges == 1
+
+
+class _SharedKeyframesStub:
+    """The three things FactorGraph touches of the reference's SharedKeyframes (mast3r_slam/frame.py:245-364):
+    T_WC [buffer,1,8], `frames[idx]` -> an object with X_canon / T_WC.data [1,8] / get_average_conf(), and
+    update_T_WCs doing `self.T_WC[idx] = T_WCs.data` (:362-364) — shapes exactly as in the reference."""
+
+    class _Pose:
+        def __init__(self, data):
+            self.data = data
+
+    class _Kf:
+        def __init__(self, X, C, T):
+            self.X_canon, self._C, self.T_WC = X, C, _SharedKeyframesStub._Pose(T)
+
+        def get_average_conf(self):
+            return self._C
+
+    def __init__(self, Xs, Cs, Twc, buffer=8):
+        self.X, self.C = Xs, Cs
+        self.T_WC = torch.zeros((buffer, 1, 8), dtype=torch.float32, device=Xs.device)
+        self.T_WC[:Twc.shape[0], 0] = Twc
+
+    def __getitem__(self, idx):
+        k = int(idx)
+        return self._Kf(self.X[k], self.C[k], self.T_WC[k])
+
+    def update_T_WCs(self, T_WCs, idx):
+        self.T_WC[idx] = T_WCs.data
+
+
+def test_adopts_shared_keyframes_shaped_frames_and_empty_attributes(fgm, synth):
+    """the non-`gather` frames branch (the reference's SharedKeyframes) with more than two keyframes, and the
+    reference's attribute names before the first add_factors (empty tensors, global_opt.py:17-25)."""
+    need_gpu()
+    ops = pkg("backends")
+    g = synth.make_graph_exact(5, 7, 2000, seed=81, noise=1e-3)
+    g = {k: (v.cuda() if torch.is_tensor(v) else v) for k, v in g.items()}
+    empty = fgm.FactorGraph(frames=None, device="cuda")
+    for name in ("ii", "jj", "idx_ii2jj", "idx_jj2ii", "valid_match_j", "valid_match_i", "Q_ii2jj", "Q_jj2ii"):
+        assert getattr(empty, name).numel() == 0
+    assert empty.num_edges == 0 and empty.get_unique_kf_idx().numel() == 0
+    frames = _SharedKeyframesStub(g["Xs"], g["Cs"], g["Twc"])
+    before = frames.T_WC.clone()
+    fg = _store_from_graph(fgm, g, frames)
+    fg.solve_GN_rays()
+    Twc_ref = g["Twc"].clone()
+    ii, jj, idx, valid, Q = fg.prep_two_way_edges()
+    c = fg.cfg
+    ops.gauss_newton_rays(Twc_ref, g["Xs"], g["Cs"], ii, jj, idx, valid, Q, c["sigma_ray"], c["sigma_dist"],
+                          c["C_conf"], c["Q_conf"], c["max_iters"], 0.0)
+    assert torch.equal(frames.T_WC[1:5, 0], Twc_ref[1:])       # k = 4 > 1 poses written back through [k,1,8]
+    assert torch.equal(frames.T_WC[0], before[0]) and torch.equal(frames.T_WC[5:], before[5:])
+    assert not torch.equal(frames.T_WC[1:5], before[1:5])
