@@ -10,6 +10,8 @@ constexpr int kPose = 7;        // Sim(3) tangent dimension
 constexpr int kAcc = 35;        // 28 upper-triangle terms of the local 7x7 + 7 gradient terms
 constexpr int kEdgeBlock = 56;  // per directed edge: A_e (49, row-major) + b_e (7), fp64
 constexpr int kTile = 32;       // Cholesky tile
+constexpr int kLlKinds = 5;     // L_kk, L_(k+1,k), tile (k+2,k+1), tile (k+2,k+2), L_(k+2,k)
+constexpr int kLlRing = 4;      // steps a slot lives before it is reused
 constexpr int kAccumThreads = 256;
 constexpr int kSolveThreads = 256;
 
@@ -52,7 +54,7 @@ struct GnLayout {
   int num_kf, num_edges, num_pts;
   int dim, nblk, ld, rows;  // system dim 7(N-1); tiles; leading dimension; rows incl. rhs tile row
   size_t off_ctrl, off_counters, off_ci, off_cj, off_bitmap, off_prefix, off_inc_off, off_inc_list,
-      off_order, off_partials, off_eb, off_hd, off_linv, off_counts, off_kloc, off_packed, off_total;
+      off_order, off_partials, off_eb, off_hd, off_linv, off_flags, off_ll, off_counts, off_kloc, off_packed, off_total;
   int edges_local;  // packed slabs are sized for this many edges (== num_edges unless sharded)
 };
 
@@ -87,6 +89,11 @@ inline GnLayout gn_layout(int num_kf, int num_edges, int num_pts, int edges_loca
   L.off_eb = take(sizeof(double) * kEdgeBlock * (size_t)num_edges);
   L.off_hd = take(sizeof(double) * (size_t)L.rows * L.ld);
   L.off_linv = take(sizeof(double) * (size_t)L.nblk * kTile * kTile);
+  // tile flags of the dataflow factorisation, three arrays of (nblk+1) x nblk: done (tile holds its final L values),
+  // rdy (helper -> chain hand-off of a diagonal / sub-diagonal tile), rdyh (cyclic owner -> helper hand-off of a band tile)
+  L.off_flags = take(sizeof(int) * 3 * (size_t)(L.nblk + 1) * L.nblk);
+  // LL transfer buffers of the chain <-> helper loop: kLlKinds tiles x ring of kLlRing steps x 2048 tagged 8-byte words
+  L.off_ll = take(sizeof(unsigned long long) * kLlKinds * kLlRing * 2 * kTile * kTile);
   // compacted per-point records of the locally owned edges (last regions): per (edge, chunk) a count,
   // then for each surviving point its chunk-local index (u16) and {int32 m, float sqrt(Q)}
   L.edges_local = edges_local < 0 ? num_edges : edges_local;
@@ -111,6 +118,8 @@ struct GnPtrs {
   double* eb;
   double* hd;
   double* linv;
+  int* flags;
+  unsigned long long* ll;
   uint2* packed;
   uint16_t* kloc;
   int* counts;
@@ -132,6 +141,8 @@ inline GnPtrs gn_ptrs(const GnLayout& L, void* ws) {
   p.eb = reinterpret_cast<double*>(b + L.off_eb);
   p.hd = reinterpret_cast<double*>(b + L.off_hd);
   p.linv = reinterpret_cast<double*>(b + L.off_linv);
+  p.flags = reinterpret_cast<int*>(b + L.off_flags);
+  p.ll = reinterpret_cast<unsigned long long*>(b + L.off_ll);
   p.packed = reinterpret_cast<uint2*>(b + L.off_packed);
   p.kloc = reinterpret_cast<uint16_t*>(b + L.off_kloc);
   p.counts = reinterpret_cast<int*>(b + L.off_counts);

@@ -260,6 +260,11 @@ struct SolveArgs {
   int32_t* info_out;
   int N, dim, nblk, ld;
   float delta_thresh;
+  // dataflow factorisation (gn_solve_df_kernel): tile flags and the P x Q grid of worker CTAs
+  int* done;
+  int* rdy;
+  unsigned long long* ll;
+  int P, Q;
 };
 
 template <bool COOP>
@@ -708,6 +713,887 @@ gn_solve_kernel(const SolveArgs a) {
   }
 }
 
+
+// =============================================================================== dataflow solver
+// gn_solve_df_kernel: the same four phases, but the factorisation (B) is a flag-driven dataflow over 32x32 tiles
+// instead of grid-wide steps.  Measured on B200 (profiles/r02a_ubench_solve.log): a grid barrier costs 1.24 us,
+// a flag hand-off through L2 0.4 us one way, a 32x32 potrf in one warp >= 3.75 us, and mma.sync.m8n8k4.f64 (DMMA)
+// runs at the full fp64 rate (36.9 TFLOP/s) with 4 warps per SM where DFMA code is bound by shared-memory operand
+// loads.  So:
+//   * CTA 0 is the CHAIN: it alone walks the critical path  potrf(k,k) -> TRSM (k+1,k) -> SYRK (k+1,k+1) -> potrf ...
+//     with every operand in its shared memory; while warp 0 factors, warps 1-3 prefetch the two tiles of the next
+//     step.  It never waits for a round trip: the only remote inputs are tiles whose owner finished them a step ago.
+//   * the other CTAs are WORKERS on a P x Q block-cyclic grid; worker (i mod P, j mod Q) OWNS tile (i,j) and applies
+//     every update to it, in column order m = 0,1,... (fixed order: bit-deterministic), then its TRSM against L_mm
+//     (forward substitution, lane = row; no explicit inverse on the path).  The last update of a diagonal tile and
+//     the TRSM of a sub-diagonal tile belong to the chain.
+//   * tile products are DMMA (4 warps x 16x16 quadrants, operands in padded shared memory: stride 36 doubles makes
+//     the 8x4 fragment loads conflict-free).
+//   * done[i][j] = tile (i,j) holds final L values; rdy[i][j] = diagonal / sub-diagonal tile has received all the
+//     updates its owner applies.  Writers: stores, __syncthreads / __syncwarp, fence, st.release.gpu; readers: one
+//     thread spins with ld.acquire.gpu, barrier, data through __ldcg (L2).  All CTAs are co-resident (cooperative
+//     launch) and every CTA consumes its tasks in (m, phase) order, so every wait points strictly backwards.
+constexpr int kDfThreads = 128;
+constexpr int kTS = 36;               // shared-memory tile row stride in doubles
+constexpr int kTileSm = kTile * kTS;  // doubles per shared-memory tile
+constexpr int kDfTiles = 7;           // tile buffers per CTA (dynamic shared memory)
+constexpr int kHelpers = 8;           // row-helper CTAs (a helper holds one row for about three steps)
+constexpr int kBand = 3;              // tiles (i,j) with i - j <= kBand are finished by helper(i) / the chain
+
+__device__ __forceinline__ int ld_acquire_gpu(const int* p) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu(int* p, int v) {
+  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void dmma_m8n8k4(double& c0, double& c1, const double a, const double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(c0), "+d"(c1)
+               : "d"(a), "d"(b));
+}
+// whole CTA
+__device__ __forceinline__ void cta_wait(const int* f) {
+  if (threadIdx.x == 0)
+    while (ld_acquire_gpu(f) == 0) {}
+  __syncthreads();
+}
+__device__ __forceinline__ void cta_wait2(const int* f, const int* g) {
+  if (threadIdx.x == 0) {
+    while (ld_acquire_gpu(f) == 0) {}
+    while (ld_acquire_gpu(g) == 0) {}
+  }
+  __syncthreads();
+}
+__device__ __forceinline__ void cta_signal(int* f) {
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) st_release_gpu(f, 1);
+}
+
+// 32x32 tile, global (row stride ld) <-> shared (row stride kTS); thread t of a group of NT
+template <int NT>
+__device__ __forceinline__ void tile_g2s(double* s, const double* g, int ld, int t) {
+  for (int q = t; q < kTile * kTile / 2; q += NT) {
+    const int r = q >> 4, c2 = (q & 15) * 2;
+    const double2 v = __ldcg(reinterpret_cast<const double2*>(g + (size_t)r * ld + c2));
+    *reinterpret_cast<double2*>(s + r * kTS + c2) = v;
+  }
+}
+template <int NT>
+__device__ __forceinline__ void tile_g2s_transposed(double* s, const double* g, int ld, int t) {
+  for (int q = t; q < kTile * kTile / 2; q += NT) {
+    const int r = q >> 4, c2 = (q & 15) * 2;
+    const double2 v = __ldcg(reinterpret_cast<const double2*>(g + (size_t)r * ld + c2));
+    s[c2 * kTS + r] = v.x;
+    s[(c2 + 1) * kTS + r] = v.y;
+  }
+}
+template <int NT>
+__device__ __forceinline__ void tile_s2g(double* g, const double* s, int ld, int t) {
+  for (int q = t; q < kTile * kTile / 2; q += NT) {
+    const int r = q >> 4, c2 = (q & 15) * 2;
+    __stcg(reinterpret_cast<double2*>(g + (size_t)r * ld + c2), *reinterpret_cast<const double2*>(s + r * kTS + c2));
+  }
+}
+
+// LL transfer of a tile through L2 WITHOUT a release fence (a fence costs the writer 1-1.5 us, r02c): every 8-byte word
+// carries a 32-bit tag next to 32 bits of payload; 8-byte accesses are single-copy atomic, so a word that shows the tag
+// holds its payload.  The buffers are zeroed at the start of every solve and a slot is reused only kLlRing steps later
+// with a different tag, so a stale word can never match.  dst/src: 2048 words; element e of the 32x32 tile = words 2e, 2e+1.
+template <int NT>
+__device__ __forceinline__ void ll_store_tile(unsigned long long* dst, const double* sT, unsigned tag, int t) {
+  const unsigned long long hi = (unsigned long long)tag << 32;
+  for (int q = t; q < kTile * kTile / 2; q += NT) {
+    const int r = q >> 4, c2 = (q & 15) * 2;
+    const double2 v = *reinterpret_cast<const double2*>(sT + r * kTS + c2);
+    const unsigned long long bx = (unsigned long long)__double_as_longlong(v.x), by = (unsigned long long)__double_as_longlong(v.y);
+    unsigned long long* w = dst + 2 * (r * kTile + c2);
+    asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(w), "l"(hi | (bx & 0xffffffffull)), "l"(hi | (bx >> 32)) : "memory");
+    asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(w + 2), "l"(hi | (by & 0xffffffffull)), "l"(hi | (by >> 32)) : "memory");
+  }
+}
+// All chunks of a thread are requested before any tag is looked at (a check per chunk would serialise one L2 round
+// trip per chunk: 16 per lane for a one-warp reader, measured 5-7 us per tile); only missing chunks are re-requested.
+template <int NT, bool TRANSPOSED>
+__device__ __forceinline__ void ll_load_tile(double* sT, const unsigned long long* src, unsigned tag, int t) {
+  // Gate: ONE thread polls one word until the tag shows, then the group reads the tile (and re-reads stragglers).  With
+  // every thread polling its own chunks the writer's stores queued behind ~16 KB of polling loads per round on the same
+  // L2 lines (r02c: a 0.3 us store took 2 us).  Group barrier: id 0 = the whole CTA, NT == 96 = warps 1-3 (id 7).
+  if (t == 0) {
+    unsigned long long w;
+    const unsigned long long* p = src + 2 * kTile * kTile - 1;
+    do {
+      asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
+    } while ((unsigned)(w >> 32) != tag);
+  }
+  if (NT == kDfThreads) __syncthreads();
+  else if (NT == 96) asm volatile("bar.sync 7, 96;" ::: "memory");
+  else __syncwarp();
+  constexpr int kChunks = kTile * kTile / 2;                // 32-byte chunks (two doubles) per tile
+  constexpr int kPer = (kChunks + NT - 1) / NT;              // chunks per thread
+  constexpr int kBatch = kPer < 4 ? kPer : 4;                // in flight per thread (register budget)
+  for (int b0 = 0; b0 < kPer; b0 += kBatch) {
+    unsigned long long w[kBatch][4];
+    unsigned pending = 0;
+#pragma unroll
+    for (int c = 0; c < kBatch; c++)
+      if (b0 + c < kPer && t + (b0 + c) * NT < kChunks) pending |= 1u << c;
+    while (pending) {
+#pragma unroll
+      for (int c = 0; c < kBatch; c++)
+        if (pending & (1u << c)) {
+          const int q = t + (b0 + c) * NT;
+          const unsigned long long* p = src + 2 * ((q >> 4) * kTile + (q & 15) * 2);
+          asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[c][0]), "=l"(w[c][1]) : "l"(p) : "memory");
+          asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[c][2]), "=l"(w[c][3]) : "l"(p + 2) : "memory");
+        }
+#pragma unroll
+      for (int c = 0; c < kBatch; c++)
+        if ((pending & (1u << c)) && (unsigned)(w[c][0] >> 32) == tag && (unsigned)(w[c][1] >> 32) == tag &&
+            (unsigned)(w[c][2] >> 32) == tag && (unsigned)(w[c][3] >> 32) == tag)
+          pending &= ~(1u << c);
+    }
+#pragma unroll
+    for (int c = 0; c < kBatch; c++) {
+      const int q = t + (b0 + c) * NT;
+      if (b0 + c < kPer && q < kChunks) {
+        const int r = q >> 4, c2 = (q & 15) * 2;
+        const double x = __longlong_as_double((long long)((w[c][1] << 32) | (w[c][0] & 0xffffffffull)));
+        const double y = __longlong_as_double((long long)((w[c][3] << 32) | (w[c][2] & 0xffffffffull)));
+        if (TRANSPOSED) {
+          sT[c2 * kTS + r] = x;
+          sT[(c2 + 1) * kTS + r] = y;
+        } else {
+          *reinterpret_cast<double2*>(sT + r * kTS + c2) = make_double2(x, y);
+        }
+      }
+    }
+  }
+}
+
+// acc (16x16 quadrant of this warp: rows r0.., cols c0..) += A * B^T, A and B 32x32 row-major in shared memory.
+// Fragments of mma.m8n8k4.f64: A[m][k]: lane (g = lane/4, t = lane%4) holds row g, column t; B[k][n] = Bmat[n][k]: the
+// same access pattern on Bmat; C: row g, columns 2t and 2t+1.
+__device__ __forceinline__ void tile_mma(const double* sA, const double* sB, int r0, int c0, int g, int t,
+                                         double (&acc)[2][2][2]) {
+#pragma unroll
+  for (int kk = 0; kk < 8; kk++) {
+    const double a0 = sA[(r0 + g) * kTS + kk * 4 + t], a1 = sA[(r0 + 8 + g) * kTS + kk * 4 + t];
+    const double b0 = sB[(c0 + g) * kTS + kk * 4 + t], b1 = sB[(c0 + 8 + g) * kTS + kk * 4 + t];
+    dmma_m8n8k4(acc[0][0][0], acc[0][0][1], a0, b0);
+    dmma_m8n8k4(acc[0][1][0], acc[0][1][1], a0, b1);
+    dmma_m8n8k4(acc[1][0][0], acc[1][0][1], a1, b0);
+    dmma_m8n8k4(acc[1][1][0], acc[1][1][1], a1, b1);
+  }
+}
+
+// X L^T = A by forward substitution, one warp, lane = row: x holds row `lane` of A on entry and of X on exit.
+// sLT[c][c2] = L[c2][c] (row c of sLT = column c of L, contiguous), rinv[c] = 1 / L[c][c].
+__device__ __forceinline__ void trsm_rows(double (&x)[kTile], const double* sLT, const double* rinv) {
+#pragma unroll
+  for (int c = 0; c < kTile; c++) {
+    const double xc = x[c] * rinv[c];
+    x[c] = xc;
+#pragma unroll
+    for (int c2 = (c + 1) & ~1; c2 < kTile; c2 += 2) {
+      const double2 v = *reinterpret_cast<const double2*>(sLT + c * kTS + c2);
+      if (c2 > c) x[c2] -= xc * v.x;
+      x[c2 + 1] -= xc * v.y;
+    }
+  }
+}
+
+// Cholesky of the 32x32 tile in sD (lower part valid) by ONE warp, lane = row, rows in registers.  Right-looking in
+// LDL^T order: per pivot the unscaled column goes through a double-buffered 32-double shared array (1 STS + 16
+// broadcast LDS.128 instead of 62 shuffles: 12.5k -> 7.4k cycles, r02a_ubench_solve.log) and the chain carries one
+// reciprocal; the square roots are applied to whole columns at the end.  Writes sL (row-major, zero upper part),
+// sLT (its transpose) and rinv[c] = 1 / L[c][c].  Returns true if a pivot was <= 0 (or NaN).
+__device__ __forceinline__ bool potrf_tile(const double* sD, double* sL, double* sLT, double* rinv, double* col, int lane) {
+  double a[kTile];
+#pragma unroll
+  for (int c = 0; c < kTile; c += 2) {
+    const double2 v = *reinterpret_cast<const double2*>(sD + lane * kTS + c);
+    a[c] = v.x;
+    a[c + 1] = v.y;
+  }
+  bool bad = false;
+  double my_d = 1.0;
+#pragma unroll
+  for (int j = 0; j < kTile; j++) {
+    double* cb = col + (j & 1) * kTile;
+    cb[lane] = a[j];
+    __syncwarp();
+    double d = cb[j];
+    if (!(d > 0.0)) {
+      bad = true;
+      d = 1.0;
+    }
+    if (lane == j) my_d = d;
+    const double tj = a[j] * (1.0 / d);
+#pragma unroll
+    for (int c = (j + 1) & ~1; c < kTile; c += 2) {
+      const double2 v = *reinterpret_cast<const double2*>(cb + c);
+      if (c > j) a[c] -= tj * v.x;
+      a[c + 1] -= tj * v.y;
+    }
+  }
+  const double rs = rsqrt(my_d);  // 1 / L[lane][lane]
+  col[lane] = rs;                 // (lower half of `col`: last used by pivot 30, every lane is past pivot 31's barrier)
+  rinv[lane] = rs;
+  __syncwarp();
+#pragma unroll
+  for (int c = 0; c < kTile; c++) {
+    const double l = (c <= lane) ? a[c] * col[c] : 0.0;
+    sL[lane * kTS + c] = l;
+    sLT[c * kTS + lane] = l;
+  }
+  return bad;
+}
+
+#ifdef M3R_SOLVE_PROF
+__device__ __forceinline__ unsigned long long gtime_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#define DFP(slot) do { if (tid == 0) { const unsigned long long n_ = gtime_ns(); prof[slot] += (float)(n_ - prof_t); prof_t = n_; if (s_raw_k >= 0 && s_raw_k < 58 && (slot) >= 2 && (slot) <= 6) s_raw[s_raw_k][(slot) - 2] = (unsigned)n_; if ((slot) == 11 && s_raw_k >= 0 && s_raw_k < 58) s_raw[s_raw_k][5] = (unsigned)n_; } } while (0)
+#else
+#define DFP(slot) do { } while (0)
+#endif
+
+__global__ void __launch_bounds__(kDfThreads, 2)
+gn_solve_df_kernel(const SolveArgs a) {
+  if (a.ctrl[CTRL_DONE]) return;  // uniform over the grid: set only by a previous launch
+  extern __shared__ __align__(16) double s_dyn[];  // kDfTiles tiles (phase B) | s_x: dimP doubles (phase C)
+  __shared__ __align__(16) double s_col[2 * kTile];
+  __shared__ double s_rinv[kTile];
+  __shared__ double s_red[kDfThreads / 32];
+  __shared__ int s_fail;
+  double* const s_x = s_dyn + kDfTiles * kTileSm;
+  cg::grid_group grid = cg::this_grid();
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int nblk = a.nblk, ld = a.ld, dim = a.dim, dimP = a.nblk * kTile;
+  double* H = a.hd;
+  const int nfree = a.N - 1;
+  if (tid == 0) s_fail = 0;
+#ifdef M3R_SOLVE_PROF
+  float prof[12] = {};
+  __shared__ unsigned s_raw[58][6];
+  int s_raw_k = -1;
+  unsigned long long prof_t = gtime_ns();
+  const unsigned long long prof_t0 = prof_t;
+#endif
+
+  // ---------------------------------------------------------------- A. assemble (+ flag reset)
+  for (int t = blockIdx.x * kDfThreads + tid; t < 3 * (nblk + 1) * nblk; t += gridDim.x * kDfThreads) a.done[t] = 0;  // done | rdy | rdyh contiguous
+  for (int t = blockIdx.x * kDfThreads + tid; t < kLlKinds * kLlRing * 2 * kTile * kTile; t += gridDim.x * kDfThreads) a.ll[t] = 0ull;
+  const int nstrips = nfree + 2;
+  for (int sidx = blockIdx.x; sidx < nstrips; sidx += gridDim.x) {
+    if (sidx < nfree) {
+      const int p = sidx;
+      const int r0 = 7 * p, ncol = 7 * p + 7;
+      for (int t = tid; t < 7 * ncol; t += kDfThreads) H[(size_t)(r0 + t / ncol) * ld + (t % ncol)] = 0.0;
+      __syncthreads();
+      const int c = p + 1;  // compact pose index
+      const int lo = a.inc_off[c], hi = a.inc_off[c + 1];
+      for (int q = lo; q < hi; q++) {
+        const int ent = a.inc_list[q];
+        const int e = ent >> 1, role = ent & 1;
+        const int other = (role == 0 ? a.cj[e] : a.ci[e]) - 1;
+        const double* blk = a.eb + (size_t)e * kEdgeBlock;
+        if (tid < 49) {
+          const int r = tid / 7, cc = tid % 7;
+          const double v = blk[tid];
+          H[(size_t)(r0 + r) * ld + (r0 + cc)] += v;
+          if (other >= 0 && other < p) H[(size_t)(r0 + r) * ld + (7 * other + cc)] -= v;
+        }
+      }
+      __syncthreads();
+    } else if (sidx == nfree) {
+      for (int t = tid; t < (dimP - dim) * ld; t += kDfThreads) {
+        const int r = dim + t / ld, cc = t % ld;
+        H[(size_t)r * ld + cc] = (r == cc) ? 1.0 : 0.0;
+      }
+    } else {
+      // rhs tile row: row dimP holds g, rows dimP+1.. are zero
+      for (int t = tid; t < kTile * ld; t += kDfThreads) H[(size_t)dimP * ld + t] = 0.0;
+      __syncthreads();
+      for (int p = tid; p < nfree; p += kDfThreads) {
+        const int c = p + 1;
+        double g[7] = {0, 0, 0, 0, 0, 0, 0};
+        for (int q = a.inc_off[c]; q < a.inc_off[c + 1]; q++) {
+          const int ent = a.inc_list[q];
+          const double* bv = a.eb + (size_t)(ent >> 1) * kEdgeBlock + 49;
+          const double sgn = (ent & 1) ? 1.0 : -1.0;  // g_i = -b_e, g_j = +b_e
+#pragma unroll
+          for (int k = 0; k < 7; k++) g[k] += sgn * bv[k];
+        }
+#pragma unroll
+        for (int k = 0; k < 7; k++) H[(size_t)dimP * ld + 7 * p + k] = g[k];
+      }
+    }
+  }
+  DFP(0);
+  grid.sync();
+  DFP(1);
+
+  // ---------------------------------------------------------------- B. Cholesky, dataflow
+  // Roles: CTA 0 = chain; CTAs 1..kHelpers = row helpers; the rest = P x Q block-cyclic workers.
+  // Who applies column m to tile (i,j) (m < j <= i), and who finishes the tile:
+  //   i - j >= 3 (far tiles)     : the cyclic owner applies every column and does the TRSM at step j
+  //   i - j <= 2 (band of row i) : columns m <= i-4 the cyclic owner (hand-off flag rdyh[i][j]);
+  //                                columns i-3 and i-2 helper(i) (tiles stay in its shared memory); it also does
+  //                                the TRSM of (i,i-2) -- ONE hop after the chain publishes L_(i-2,i-2) -- and hands
+  //                                (i,i-1) and (i,i) to the chain (rdy[i][j]);
+  //                                column i-1: the chain (TRSM of (i,i-1), SYRK on (i,i), potrf).
+  // Measured motivation (r02b): with every near-diagonal tile two L2 hops away (worker TRSM -> worker update -> chain,
+  // ~2.2 us per hop: store, release fence, poll, load) the chain idled 10-15 us per step waiting for its inputs.
+  const int P = a.P, Q = a.Q;
+  const size_t nflag = (size_t)(nblk + 1) * nblk;
+  int* const rdyh = a.rdy + nflag;
+  double* const s_tiles = s_dyn;
+  auto gtile = [&](int i, int j) -> double* { return &H[(size_t)(i * kTile) * ld + j * kTile]; };
+  // LL slot of kind (0: L_kk, 1: L_(k+1,k), 2: tile (k+2,k+1), 3: tile (k+2,k+2)) written at step k; its tag is k+1
+  auto llslot = [&](int kind, int k) -> unsigned long long* { return a.ll + (size_t)(kind * kLlRing + (k & (kLlRing - 1))) * 2 * kTile * kTile; };
+  // dst (shared, 4 warps) -= A * B^T
+  auto smem_gemm_sub = [&](double* dst, const double* A, const double* B) {
+    const int g = lane >> 2, t4 = lane & 3, r0 = (warp >> 1) * 16, c0 = (warp & 1) * 16;
+    double acc[2][2][2] = {};
+    tile_mma(A, B, r0, c0, g, t4, acc);
+#pragma unroll
+    for (int mi = 0; mi < 2; mi++)
+#pragma unroll
+      for (int ni = 0; ni < 2; ni++) {
+        double2* d = reinterpret_cast<double2*>(dst + (r0 + mi * 8 + g) * kTS + c0 + ni * 8 + 2 * t4);
+        double2 v = *d;
+        v.x -= acc[mi][ni][0];
+        v.y -= acc[mi][ni][1];
+        *d = v;
+      }
+  };
+  // rows of the tile in `sT` <- rows * L^-T (warp 0 only; sLT / s_rinv describe L)
+  auto trsm_tile_inplace = [&](double* sT, const double* sLT_) {
+    double x[kTile];
+#pragma unroll
+    for (int c = 0; c < kTile; c += 2) {
+      const double2 v = *reinterpret_cast<const double2*>(sT + lane * kTS + c);
+      x[c] = v.x;
+      x[c + 1] = v.y;
+    }
+    trsm_rows(x, sLT_, s_rinv);
+#pragma unroll
+    for (int c = 0; c < kTile; c += 2) *reinterpret_cast<double2*>(sT + lane * kTS + c) = make_double2(x[c], x[c + 1]);
+  };
+  if (blockIdx.x == 0) {
+    // ------------------------------------------------ chain
+    // warps 0-2 compute (warp 0: potrf and TRSM; all three: the SYRK), warp 3 is the I/O warp: it fetches the two tiles of
+    // the next step and publishes L_kk / L_(k+1,k).  A release store blocks its thread for 1-1.5 us (the fence waits for
+    // the L2 write acknowledgements), so the compute warps never wait for it: the hand-overs are split named barriers
+    //   bar 1 (128)  sync, both sides        : fetch of step k done  <->  potrf(k) done (sL complete)
+    //   bar 2 (96)   sync, compute warps     : TRSM done -> SYRK
+    //   bar 5 (64)   warp 0 ARRIVE, I/O sync  : TRSM done, sP final (I/O may send it)
+    //   bar 4 (64)   I/O ARRIVE, warp 0 sync  : I/O has read sL (potrf(k+1) may overwrite it)
+    // The three transfers of the chain <-> helper loop (L_kk and L_(k+1,k) out, the next two tiles in) are LL, fence-free.
+    double* sL = s_tiles;
+    double* sLT = s_tiles + kTileSm;
+    double* sPb[2] = {s_tiles + 2 * kTileSm, s_tiles + 3 * kTileSm};
+    double* sDb[2] = {s_tiles + 4 * kTileSm, s_tiles + 5 * kTileSm};  // diagonal tile of step k: sDb[k & 1]
+    tile_g2s<kDfThreads>(sDb[0], H, ld, tid);
+    __syncthreads();
+    // The two tiles of step k -- (k+1,k) and (k+1,k+1), each with columns <= k-1 applied -- fetched by warps 1-3 (thread
+    // t of 96) while warp 0 factors: helper(k+1) sent them at step k-1 (LL, tag k); step 0 reads the assembled matrix.
+    auto chain_fetch = [&](int k, double* sP_, double* sDn_, int t) {
+      if (k >= 1) ll_load_tile<96, false>(sP_, llslot(2, k - 1), (unsigned)k, t);
+      else tile_g2s<96>(sP_, gtile(1, 0), ld, t);
+      if (k + 1 < nblk) {
+        if (k >= 1) ll_load_tile<96, false>(sDn_, llslot(3, k - 1), (unsigned)k, t);
+        else tile_g2s<96>(sDn_, gtile(1, 1), ld, t);
+      }
+    };
+    if (warp == 3) {
+#ifdef M3R_SOLVE_PROF
+      float ip[10] = {};
+      unsigned long long ip_t = gtime_ns();
+#define IOP(slot) do { __syncwarp(); if (lane == 0) { const unsigned long long n_ = gtime_ns(); ip[slot] += (float)(n_ - ip_t); ip_t = n_; } } while (0)
+#else
+#define IOP(slot) do { } while (0)
+#endif
+      for (int k = 0; k < nblk; k++) {
+        double* sP = sPb[k & 1];
+        double* sDn = sDb[(k + 1) & 1];
+        chain_fetch(k, sP, sDn, 64 + lane);
+        IOP(1);
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        IOP(2);
+        ll_store_tile<96>(llslot(0, k), sL, (unsigned)(k + 1), 64 + lane);  // L_kk -> helper(k+2), no fence
+        IOP(3);
+        tile_s2g<32>(gtile(k, k), sL, ld, lane);
+        if (k + 1 < nblk) asm volatile("bar.arrive 4, 64;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) st_release_gpu(&a.done[k * nblk + k], 1);  // everyone else reads L_kk from H behind this flag
+        IOP(4);
+        asm volatile("bar.sync 5, 64;" ::: "memory");                   // TRSM done
+        IOP(5);
+        ll_store_tile<32>(llslot(1, k), sP, (unsigned)(k + 1), lane);  // L_(k+1,k) -> helper(k+2)
+        IOP(6);
+        tile_s2g<32>(gtile(k + 1, k), sP, ld, lane);
+        __syncwarp();
+        if (lane == 0) st_release_gpu(&a.done[(k + 1) * nblk + k], 1);
+        __syncwarp();
+        IOP(7);
+      }
+#ifdef M3R_SOLVE_PROF
+      if (lane == 0 && a.ctrl[CTRL_ITERS] == 0)
+        printf("DFIO: LL-load S %.1f, LL-load D %.1f, wait potrf %.1f, LL-store L %.1f, store L + release %.1f, wait trsm %.1f, LL-store P %.1f, "
+               "store P + release %.1f us\n", ip[0] * 1e-3f, ip[1] * 1e-3f, ip[2] * 1e-3f, ip[3] * 1e-3f, ip[4] * 1e-3f, ip[5] * 1e-3f, ip[6] * 1e-3f, ip[7] * 1e-3f);
+#endif
+    } else {
+      for (int k = 0; k < nblk; k++) {
+#ifdef M3R_SOLVE_PROF
+        s_raw_k = k;
+#endif
+        double* sP = sPb[k & 1];
+        if (warp == 0) {
+          if (k >= 1) asm volatile("bar.sync 4, 64;" ::: "memory");
+          DFP(3);
+          if (potrf_tile(sDb[k & 1], sL, sLT, s_rinv, s_col, lane) && lane == 0) s_fail = 1;
+          DFP(5);
+        } else {
+          chain_fetch(k, sP, sDb[(k + 1) & 1], (warp - 1) * 32 + lane);  // idle during the factorisation: help the I/O warp
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        DFP(2);
+        if (warp == 0) {
+          trsm_tile_inplace(sP, sLT);
+          asm volatile("bar.arrive 5, 64;" ::: "memory");
+        } else {
+          ll_store_tile<96>(llslot(0, k), sL, (unsigned)(k + 1), (warp - 1) * 32 + lane);  // (idle during the TRSM)
+        }
+        asm volatile("bar.sync 2, 96;" ::: "memory");
+        DFP(4);
+        if (k + 1 < nblk) {
+          // last update of the next diagonal tile: sDn -= L_(k+1,k) L_(k+1,k)^T; 16 8x8 output tiles over 3 warps
+          double* sDn = sDb[(k + 1) & 1];
+          const int g = lane >> 2, t4 = lane & 3;
+          // (6 / 5 / 5 output tiles per warp, all accumulators live: the 8 dependent DMMAs of a tile interleave with the others')
+          double acc[6][2];
+#pragma unroll
+          for (int q = 0; q < 6; q++) acc[q][0] = acc[q][1] = 0.0;
+#pragma unroll
+          for (int kk = 0; kk < 8; kk++) {
+#pragma unroll
+            for (int q = 0; q < 6; q++) {
+              const int ot = warp + 3 * q;
+              if (ot < 16) {
+                const int r0 = (ot >> 2) * 8, c0 = (ot & 3) * 8;
+                dmma_m8n8k4(acc[q][0], acc[q][1], sP[(r0 + g) * kTS + kk * 4 + t4], sP[(c0 + g) * kTS + kk * 4 + t4]);
+              }
+            }
+          }
+#pragma unroll
+          for (int q = 0; q < 6; q++) {
+            const int ot = warp + 3 * q;
+            if (ot < 16) {
+              const int r0 = (ot >> 2) * 8, c0 = (ot & 3) * 8;
+              double2* d = reinterpret_cast<double2*>(sDn + (r0 + g) * kTS + c0 + 2 * t4);
+              double2 v = *d;
+              v.x -= acc[q][0];
+              v.y -= acc[q][1];
+              *d = v;
+            }
+          }
+          asm volatile("bar.sync 2, 96;" ::: "memory");
+          DFP(6);
+        }
+      }
+    }
+    __syncthreads();
+  } else if ((int)blockIdx.x <= kHelpers) {
+    // ------------------------------------------------ row helper h: rows r = h (mod kHelpers), r >= 2
+    // Row r's band tiles (r, r-3 .. r) live in this CTA's shared memory while it applies the last three columns:
+    //   stage 0, column r-4: far operand L_(r,r-4) from its cyclic owner (flag: two fenced hops behind the chain, which
+    //            is why it gets two steps of slack), the other operands from H behind their flags;
+    //   stage 1, column r-3: own TRSM of (r,r-3) with L_mm by LL; operands: chain's L_(m+1,m) (LL), helper(r-1)'s
+    //            stage-2 output L_(r-1,m) (LL);
+    //   stage 2, column r-2: own TRSM of (r,r-2) (LL), chain's L_(m+1,m) (LL); tiles (r,r-1), (r,r) go to the chain by LL.
+    const int h = (int)blockIdx.x - 1;
+    double* sBd[4] = {s_tiles, s_tiles + kTileSm, s_tiles + 2 * kTileSm, s_tiles + 3 * kTileSm};  // (r,r-3) .. (r,r)
+    double* sLT = s_tiles + 4 * kTileSm;
+    double* sX = s_tiles + 5 * kTileSm;
+    double* sY = s_tiles + 6 * kTileSm;
+#ifdef M3R_SOLVE_PROF
+    float hp[10] = {};
+    unsigned long long hp_t = gtime_ns();
+#define HP(slot) do { if (tid == 0) { const unsigned long long n_ = gtime_ns(); hp[slot] += (float)(n_ - hp_t); hp_t = n_; } } while (0)
+#else
+#define HP(slot) do { } while (0)
+#endif
+    for (int r = h; r <= nblk; r += kHelpers) {
+      if (r < 2) continue;
+      const bool has_diag = r < nblk;
+      HP(9);
+      // band tiles with every column the cyclic owners apply (m <= r-5); tile q is (r, r-3+q)
+      if (r >= 5) {
+        if (tid == 0)
+          for (int q = 0; q < 4; q++)
+            if (r - 3 + q < nblk)
+              while (ld_acquire_gpu(&rdyh[r * nblk + r - 3 + q]) == 0) {}
+        __syncthreads();
+      }
+      HP(0);
+      for (int q = 0; q < 4; q++)
+        if (r - 3 + q >= 0 && r - 3 + q < nblk) tile_g2s<kDfThreads>(sBd[q], gtile(r, r - 3 + q), ld, tid);
+      if (r >= 4) {
+        // stage 0: column m = r-4
+        const int m = r - 4;
+        if (tid < 4) {  // the far operand and the three older ones: poll in parallel
+          const int j = tid == 0 ? r : r - 4 + tid;  // r, r-3, r-2, r-1
+          while (ld_acquire_gpu(&a.done[j * nblk + m]) == 0) {}
+        }
+        __syncthreads();
+        HP(1);
+        tile_g2s<kDfThreads>(sX, gtile(r, m), ld, tid);
+        tile_g2s<kDfThreads>(sY, gtile(r - 3, m), ld, tid);
+        tile_g2s<kDfThreads>(sLT, gtile(r - 2, m), ld, tid);  // (sLT is free until stage 1)
+        __syncthreads();
+        smem_gemm_sub(sBd[0], sX, sY);
+        smem_gemm_sub(sBd[1], sX, sLT);
+        if (has_diag) smem_gemm_sub(sBd[3], sX, sX);
+        __syncthreads();
+        tile_g2s<kDfThreads>(sY, gtile(r - 1, m), ld, tid);
+        __syncthreads();
+        smem_gemm_sub(sBd[2], sX, sY);
+        __syncthreads();
+        HP(2);
+      }
+      if (r >= 3) {
+        // stage 1: column m = r-3
+        const int m = r - 3;
+        ll_load_tile<kDfThreads, true>(sLT, llslot(0, m), (unsigned)(m + 1), tid);  // L_mm^T
+        __syncthreads();
+        if (tid < kTile) s_rinv[tid] = 1.0 / sLT[tid * kTS + tid];
+        __syncthreads();
+        HP(3);
+        if (warp == 0) trsm_tile_inplace(sBd[0], sLT);                                // L_(r,m)
+        else ll_load_tile<96, false>(sY, llslot(1, m), (unsigned)(m + 1), tid - 32);  // meanwhile: the chain's L_(m+1,m)
+        __syncthreads();
+        smem_gemm_sub(sBd[1], sBd[0], sY);  // (r, r-2)
+        __syncthreads();
+        ll_load_tile<kDfThreads, false>(sY, llslot(4, m), (unsigned)(m + 1), tid);  // helper(r-1)'s L_(r-1,m)
+        tile_s2g<kDfThreads>(gtile(r, m), sBd[0], ld, tid);                           // L_(r,m) for everyone else
+        __syncthreads();
+        smem_gemm_sub(sBd[2], sBd[0], sY);  // (r, r-1)
+        if (has_diag) smem_gemm_sub(sBd[3], sBd[0], sBd[0]);
+        __syncthreads();
+        if (tid == 0) st_release_gpu(&a.done[r * nblk + m], 1);  // (last: the fence blocks its warp for > 1 us)
+        HP(4);
+      }
+      {
+        // stage 2: column m = r-2, one LL hop behind the chain
+        const int m = r - 2;
+        ll_load_tile<kDfThreads, true>(sLT, llslot(0, m), (unsigned)(m + 1), tid);  // L_mm^T
+        __syncthreads();
+        HP(5);
+        if (tid < kTile) s_rinv[tid] = 1.0 / sLT[tid * kTS + tid];
+        __syncthreads();
+        if (warp == 0) trsm_tile_inplace(sBd[1], sLT);                                // L_(r,m)
+        else ll_load_tile<96, false>(sY, llslot(1, m), (unsigned)(m + 1), tid - 32);  // meanwhile: the chain's L_(m+1,m)
+        __syncthreads();
+        HP(6);
+        smem_gemm_sub(sBd[2], sBd[1], sY);
+        __syncthreads();
+        ll_store_tile<kDfThreads>(llslot(2, m), sBd[2], (unsigned)(m + 1), tid);  // tile (r,r-1) -> chain
+        if (has_diag) {
+          smem_gemm_sub(sBd[3], sBd[1], sBd[1]);
+          __syncthreads();
+          ll_store_tile<kDfThreads>(llslot(3, m), sBd[3], (unsigned)(m + 1), tid);  // tile (r,r) -> chain
+        }
+        ll_store_tile<kDfThreads>(llslot(4, m), sBd[1], (unsigned)(m + 1), tid);  // L_(r,m) -> helper(r+1), stage 1
+        HP(7);
+        tile_s2g<kDfThreads>(gtile(r, m), sBd[1], ld, tid);  // ... and for everyone else, behind a flag
+        __syncthreads();
+        if (tid == 0) st_release_gpu(&a.done[r * nblk + m], 1);
+        __syncthreads();
+        HP(8);
+      }
+    }
+#ifdef M3R_SOLVE_PROF
+    if (tid == 0 && a.ctrl[CTRL_ITERS] == 0 && h < 2)
+      printf("DFHELP %d: wait rdyh %.1f | stage0: wait far L(r,m) %.1f, rest %.1f | stage1: wait LL L_mm %.1f, rest %.1f | stage2: wait LL L_mm %.1f, "
+             "trsm + wait LL P %.1f, gemms + LL sends %.1f, store + release %.1f | other %.1f us\n", h, hp[0] * 1e-3f, hp[1] * 1e-3f, hp[2] * 1e-3f, hp[3] * 1e-3f,
+             hp[4] * 1e-3f, hp[5] * 1e-3f, hp[6] * 1e-3f, hp[7] * 1e-3f, hp[8] * 1e-3f, hp[9] * 1e-3f);
+#endif
+  } else if ((int)blockIdx.x - 1 - kHelpers < P * Q) {
+    // ------------------------------------------------ worker (wr, wc): owns tiles i % P == wr, j % Q == wc
+    const int w = (int)blockIdx.x - 1 - kHelpers, wr = w / Q, wc = w % Q;
+    double* sLT = s_tiles;
+    double* sW = s_tiles + kTileSm;  // 4 per-warp tiles (TRSM phase) / operands A, B (update phase)
+    // one update task: tile (i,j) -= L_im L_jm^T, destination read-modify-written in global memory (L2)
+    auto update_task = [&](int i, int j, int m) {
+      const bool diag = (i == j);
+      double* sA = sW;
+      double* sBm = sW + kTileSm;
+      cta_wait2(&a.done[i * nblk + m], &a.done[j * nblk + m]);
+      tile_g2s<kDfThreads>(sA, gtile(i, m), ld, tid);
+      if (!diag) tile_g2s<kDfThreads>(sBm, gtile(j, m), ld, tid);
+      const int g = lane >> 2, t4 = lane & 3, r0 = (warp >> 1) * 16, c0 = (warp & 1) * 16;
+      double* gd = gtile(i, j);
+      double2 dst[2][2];
+#pragma unroll
+      for (int mi = 0; mi < 2; mi++)
+#pragma unroll
+        for (int ni = 0; ni < 2; ni++)
+          dst[mi][ni] = __ldcg(reinterpret_cast<const double2*>(gd + (size_t)(r0 + mi * 8 + g) * ld + c0 + ni * 8 + 2 * t4));
+      __syncthreads();
+      double acc[2][2][2] = {};
+      tile_mma(sA, diag ? sA : sBm, r0, c0, g, t4, acc);
+#pragma unroll
+      for (int mi = 0; mi < 2; mi++)
+#pragma unroll
+        for (int ni = 0; ni < 2; ni++)
+          __stcg(reinterpret_cast<double2*>(gd + (size_t)(r0 + mi * 8 + g) * ld + c0 + ni * 8 + 2 * t4),
+                 make_double2(dst[mi][ni].x - acc[mi][ni][0], dst[mi][ni].y - acc[mi][ni][1]));
+      __syncthreads();  // operands are overwritten by the next task; every store of this tile is issued
+      if (i - j <= kBand && m == i - kBand - 2 && tid == 0) st_release_gpu(&rdyh[i * nblk + j], 1);  // hand-off to helper(i)
+    };
+    for (int m = 0; m < nblk; m++) {
+      // ---- column m: TRSM of the owned far tiles (i,m), i >= m+3, and L_mm^-1 (for phase C) if (m,m) is owned
+      if (m % Q == wc) {
+        const int i0 = m + ((wr - m % P) + P) % P;  // first i >= m with i % P == wr
+        bool any = false;
+        for (int i = i0; i <= nblk; i += P) any = any || (i == m || i > m + kBand);
+        if (any) {
+          cta_wait(&a.done[m * nblk + m]);
+          tile_g2s_transposed<kDfThreads>(sLT, gtile(m, m), ld, tid);
+          __syncthreads();
+          if (tid < kTile) s_rinv[tid] = 1.0 / sLT[tid * kTS + tid];
+          __syncthreads();
+          int q = 0;
+          for (int i = i0; i <= nblk; i += P) {
+            if (i > m && i <= m + kBand) continue;  // chain / helper
+            if (((q++) & 3) != warp) continue;
+            double* sT = sW + warp * kTileSm;
+            double* gt = gtile(i, m);
+            double x[kTile];
+            if (i == m) {
+#pragma unroll
+              for (int c = 0; c < kTile; c++) x[c] = (c == lane) ? 1.0 : 0.0;
+            } else {
+              __syncwarp();
+              tile_g2s<32>(sT, gt, ld, lane);
+              __syncwarp();
+#pragma unroll
+              for (int c = 0; c < kTile; c += 2) {
+                const double2 v = *reinterpret_cast<const double2*>(sT + lane * kTS + c);
+                x[c] = v.x;
+                x[c + 1] = v.y;
+              }
+            }
+            trsm_rows(x, sLT, s_rinv);
+            if (i == m) {
+              // x = row `lane` of L^-T, i.e. column `lane` of L^-1: linv[c][lane] (row-major L^-1, as phase C reads it)
+#pragma unroll
+              for (int c = 0; c < kTile; c++) a.linv[(size_t)m * kTile * kTile + c * kTile + lane] = x[c];
+            } else {
+              __syncwarp();
+#pragma unroll
+              for (int c = 0; c < kTile; c += 2) *reinterpret_cast<double2*>(sT + lane * kTS + c) = make_double2(x[c], x[c + 1]);
+              __syncwarp();
+              tile_s2g<32>(gt, sT, ld, lane);
+              __syncwarp();
+              if (lane == 0) st_release_gpu(&a.done[i * nblk + m], 1);
+            }
+          }
+          __syncthreads();
+        }
+      }
+      // ---- updates.  A tile's column-c update is LAGGED one step (done in phase c+1) unless it is the last one before the
+      // tile's TRSM / hand-off: the on-time updates (whose operands were published moments ago) then never queue behind
+      // bulk work, and the bulk work only needs operands that are a whole step old (no stall).  Per tile the columns are
+      // still applied in ascending order.
+      {  // (1) far tiles of column j = m+1 (their TRSM is next phase): lagged column m-1, then column m
+        const int j = m + 1;
+        if (j < nblk && j % Q == wc)
+          for (int i = j + ((wr - j % P) + P) % P; i <= nblk; i += P)
+            if (i - j > kBand) {
+              if (m >= 1) update_task(i, j, m - 1);
+              update_task(i, j, m);
+            }
+      }
+      {  // (2) hand-offs of this phase: band tiles of row m+kBand+2
+        const int i = m + kBand + 2;
+        if (i <= nblk && i % P == wr)
+          for (int j = i - kBand; j <= i && j < nblk; j++)
+            if (j % Q == wc) {
+              if (m >= 1) update_task(i, j, m - 1);
+              update_task(i, j, m);
+            }
+      }
+      if (m >= 1) {  // (3) everything else: lagged column m-1
+        const int j0 = (m + 2) + ((wc - (m + 2) % Q) + Q) % Q;
+        for (int j = j0; j < nblk; j += Q) {
+          const int ii0 = j + ((wr - j % P) + P) % P;
+          for (int i = ii0; i <= nblk; i += P) {
+            if (i - j <= kBand && i < m + kBand + 3) continue;  // band tile at or past its hand-off
+            update_task(i, j, m - 1);
+          }
+        }
+      }
+    }
+  }
+  DFP(7);
+  grid.sync();
+  DFP(8);
+  const bool failed = s_fail != 0;  // (only CTA 0, the chain, can have set it; only CTA 0 uses it below)
+
+  // ---------------------------------------------------------------- C. back-substitution  L^T x = y
+  constexpr int kRG = kDfThreads / 32;  // row groups per tile
+  constexpr int kRP = kTile / kRG;      // rows per group
+  const bool par_back = nblk >= 2 && nblk <= (int)gridDim.x;
+  if (par_back) {
+    // column-block dataflow (see gn_solve_kernel): CTA kb owns x_kb, the x_j travel as {flag | half} words
+    const int kb = blockIdx.x;
+    if (kb >= nblk) return;
+    unsigned long long* xw = reinterpret_cast<unsigned long long*>(&H[(size_t)(dimP + 2) * ld]);
+    const unsigned long long flag = 0x5A5A0001ull << 32;
+    double* red = s_dyn;               // [kRG][32] partial sums
+    double* sLi = s_dyn + kTileSm;     // L_kk^-1, row-major stride kTS
+    for (int t = tid; t < kTile * kTile; t += kDfThreads)
+      sLi[(t >> 5) * kTS + (t & 31)] = __ldcg(&a.linv[(size_t)kb * kTile * kTile + t]);
+    if (tid < kTile) s_x[kb * kTile + tid] = __ldcg(&H[(size_t)dimP * ld + kb * kTile + tid]);  // y_kb
+    const int c = tid & 31, rg = tid >> 5;
+    double tile[kRP];
+    if (kb + 1 < nblk) {
+#pragma unroll
+      for (int q = 0; q < kRP; q++) tile[q] = __ldcg(&H[(size_t)((nblk - 1) * kTile + rg * kRP + q) * ld + kb * kTile + c]);
+    }
+    __syncthreads();
+    for (int j = nblk - 1; j > kb; j--) {
+      double cur[kRP];
+#pragma unroll
+      for (int q = 0; q < kRP; q++) cur[q] = tile[q];
+      if (j - 1 > kb) {  // next tile in flight while we wait for x_j
+#pragma unroll
+        for (int q = 0; q < kRP; q++) tile[q] = __ldcg(&H[(size_t)((j - 1) * kTile + rg * kRP + q) * ld + kb * kTile + c]);
+      }
+      if (tid < 2 * kTile) {
+        unsigned long long wv;
+        const unsigned long long* src = xw + (size_t)j * 2 * kTile + tid;
+        while (true) {
+          asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(wv) : "l"(src) : "memory");
+          if ((wv >> 32) == (flag >> 32)) break;
+        }
+        reinterpret_cast<unsigned*>(&s_x[j * kTile])[tid] = (unsigned)wv;  // word 2r = low half, 2r+1 = high half
+      }
+      __syncthreads();
+      double part = 0.0;
+#pragma unroll
+      for (int q = 0; q < kRP; q++) part += cur[q] * s_x[j * kTile + rg * kRP + q];
+      red[rg * kTile + c] = part;
+      __syncthreads();
+      if (tid < kTile) {
+        double sum = 0.0;
+#pragma unroll
+        for (int g = 0; g < kRG; g++) sum += red[g * kTile + tid];
+        s_x[kb * kTile + tid] -= sum;
+      }
+      __syncthreads();
+    }
+    double xv = 0.0;
+    if (tid < kTile)
+      for (int m = tid; m < kTile; m++) xv += sLi[m * kTS + tid] * s_x[kb * kTile + m];
+    __syncthreads();
+    if (tid < kTile) {
+      s_x[kb * kTile + tid] = xv;
+      const unsigned long long bits = (unsigned long long)__double_as_longlong(xv);
+      unsigned long long* dstw = xw + (size_t)kb * 2 * kTile + 2 * tid;
+      asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(dstw), "l"(flag | (bits & 0xffffffffull)) : "memory");
+      asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(dstw + 1), "l"(flag | (bits >> 32)) : "memory");
+    }
+    __syncthreads();
+    if (blockIdx.x != 0) return;
+  } else {
+    if (blockIdx.x != 0) return;
+    for (int t = tid; t < dimP; t += kDfThreads) s_x[t] = __ldcg(&H[(size_t)dimP * ld + t]);  // y = L^-1 g
+    __syncthreads();
+    for (int kb = nblk - 1; kb >= 0; kb--) {
+      double xv = 0.0;
+      if (tid < kTile) {
+        const double* Li = a.linv + (size_t)kb * kTile * kTile;
+        for (int m = tid; m < kTile; m++) xv += __ldcg(&Li[m * kTile + tid]) * s_x[kb * kTile + m];
+      }
+      __syncthreads();
+      if (tid < kTile) s_x[kb * kTile + tid] = xv;
+      __syncthreads();
+      for (int col = tid; col < kb * kTile; col += kDfThreads) {
+        double sacc = 0.0;
+#pragma unroll 8
+        for (int r = 0; r < kTile; r++) sacc += __ldcg(&H[(size_t)(kb * kTile + r) * ld + col]) * s_x[kb * kTile + r];
+        s_x[col] -= sacc;
+      }
+      __syncthreads();
+    }
+  }
+
+  DFP(9);
+  // ---------------------------------------------------------------- D. dx, retraction, stop test
+  double ss = 0.0;
+  for (int t = tid; t < dim; t += kDfThreads) {
+    const float d = failed ? 0.0f : (float)(-s_x[t]);
+    a.dx_out[t] = d;
+    ss += (double)d * (double)d;
+  }
+  for (int off = 16; off > 0; off >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, off);
+  if ((tid & 31) == 0) s_red[tid >> 5] = ss;
+  __syncthreads();
+  for (int k = 1 + tid; k < a.N; k += kDfThreads) {
+    float T[8], xi[7];
+#pragma unroll
+    for (int c = 0; c < 8; c++) T[c] = a.Twc[(size_t)k * 8 + c];
+#pragma unroll
+    for (int c = 0; c < 7; c++) xi[c] = failed ? 0.0f : (float)(-s_x[(k - 1) * 7 + c]);
+    sim3_retract(xi, T);
+#pragma unroll
+    for (int c = 0; c < 8; c++) a.Twc[(size_t)k * 8 + c] = T[c];
+  }
+  if (tid == 0) {
+    double tot = 0.0;
+    for (int w = 0; w < kDfThreads / 32; w++) tot += s_red[w];
+    const float nrm = (float)sqrt(tot);
+    a.ctrl[CTRL_ITERS] += 1;
+    if (failed) a.ctrl[CTRL_FAILS] += 1;
+    if (nrm < a.delta_thresh) {
+      a.ctrl[CTRL_DONE] = 1;
+      a.ctrl[CTRL_EARLY] = 1;
+    }
+    if (a.info_out) {
+      a.info_out[0] = a.ctrl[CTRL_ITERS];
+      a.info_out[1] = a.ctrl[CTRL_FAILS];
+      a.info_out[2] = a.ctrl[CTRL_EARLY];
+      a.info_out[3] = a.ctrl[CTRL_BAD];
+    }
+#ifdef M3R_SOLVE_PROF
+    prof[10] = (float)(gtime_ns() - prof_t);
+    if (a.ctrl[CTRL_ITERS] == 1)
+      printf("DFPROF nblk %d grid %d P %d Q %d | assemble %.1f barrier %.1f | chain: wait-fetch(bar1) %.1f wait-bar4 %.1f trsm %.1f potrf %.1f "
+             "syrk %.1f wait-workers-end %.1f | barrier %.1f backsub %.1f tail %.1f | total %.1f us\n",
+             nblk, (int)gridDim.x, P, Q, prof[0] * 1e-3f, prof[1] * 1e-3f, prof[2] * 1e-3f, prof[3] * 1e-3f, prof[4] * 1e-3f, prof[5] * 1e-3f,
+             prof[6] * 1e-3f, prof[7] * 1e-3f, prof[8] * 1e-3f, prof[9] * 1e-3f, prof[10] * 1e-3f, (float)(gtime_ns() - prof_t0) * 1e-3f);
+    if (a.ctrl[CTRL_ITERS] == 1) {
+      printf("DFPROF signalL total %.1f us\n", prof[11] * 1e-3f);
+      for (int k = 0; k < nblk && k < 58; k += 5)
+        printf("DFRAW k %d: potrf-done +0, storeL %lld, signalL %lld, trsm %lld, pubP %lld, syrk %lld | next potrf-done %lld (ns)\n", k,
+               (long long)(s_raw[k][1] - s_raw[k][0]), (long long)(s_raw[k][5] - s_raw[k][0]), (long long)(s_raw[k][2] - s_raw[k][0]),
+               (long long)(s_raw[k][3] - s_raw[k][0]), (long long)(s_raw[k][4] - s_raw[k][0]),
+               k + 1 < nblk && k + 1 < 58 ? (long long)(s_raw[k + 1][0] - s_raw[k][0]) : 0ll);
+    }
+#endif
+  }
+}
+
 // one CTA: systems with dim <= kSmallDim when the solve cannot ride in the accumulate kernel
 // (sharded runs: the all-reduce sits between the two; or the stand-alone m3r_gn_solve_retract call)
 __global__ void __launch_bounds__(kSolveThreads)
@@ -729,35 +1615,83 @@ int launch_gn_prepare(const int64_t* ii, const int64_t* jj, const GnLayout& L, c
   return M3R_OK;
 }
 
-int launch_gn_solve(float* Twc, const GnLayout& L, const GnPtrs& P, float delta_thresh, float* dx_out,
+int launch_gn_solve(float* Twc, const GnLayout& L, const GnPtrs& P_, float delta_thresh, float* dx_out,
                     int32_t* info_out, cudaStream_t s) {
   SolveArgs a{};
-  a.Twc = Twc; a.eb = P.eb; a.ci = P.ci; a.cj = P.cj; a.inc_off = P.inc_off; a.inc_list = P.inc_list;
-  a.hd = P.hd; a.linv = P.linv; a.ctrl = P.ctrl; a.dx_out = dx_out; a.info_out = info_out;
+  a.Twc = Twc; a.eb = P_.eb; a.ci = P_.ci; a.cj = P_.cj; a.inc_off = P_.inc_off; a.inc_list = P_.inc_list;
+  a.hd = P_.hd; a.linv = P_.linv; a.ctrl = P_.ctrl; a.dx_out = dx_out; a.info_out = info_out;
   a.N = L.num_kf; a.dim = L.dim; a.nblk = L.nblk; a.ld = L.ld; a.delta_thresh = delta_thresh;
   const size_t dyn = sizeof(double) * (size_t)L.nblk * kTile;
   if (dyn > 160 * 1024) return M3R_ERR_UNSUPPORTED;  // > 20k unknowns: out of scope for a dense solve
   if (L.dim <= kSmallDim) {
     SmallSolveArgs ss{};
-    ss.Twc = Twc; ss.eb = P.eb; ss.ci = P.ci; ss.cj = P.cj; ss.inc_off = P.inc_off; ss.inc_list = P.inc_list;
-    ss.ctrl = P.ctrl; ss.dx_out = dx_out; ss.info_out = info_out; ss.N = L.num_kf; ss.dim = L.dim;
+    ss.Twc = Twc; ss.eb = P_.eb; ss.ci = P_.ci; ss.cj = P_.cj; ss.inc_off = P_.inc_off; ss.inc_list = P_.inc_list;
+    ss.ctrl = P_.ctrl; ss.dx_out = dx_out; ss.info_out = info_out; ss.N = L.num_kf; ss.dim = L.dim;
     ss.delta_thresh = delta_thresh;
     gn_small_solve_kernel<<<1, kSolveThreads, small_solve_smem_bytes(L.dim), s>>>(ss);
     M3R_LAUNCH_CHECK();
     return M3R_OK;
   }
+  // M3R_SOLVE=df: the experimental dataflow factorisation (gn_solve_df_kernel).  Parity-green, but on B200 its chain <->
+  // helper <-> worker hand-offs (0.4 us per L2 hop, 1-1.5 us per release fence) keep it at or behind the grid-step
+  // kernel (profiles/r02c_*): opt-in only.
+  static const bool use_df = [] {
+    const char* e = getenv("M3R_SOLVE");
+    return e && e[0] == 'd' && e[1] == 'f';
+  }();
+  if (use_df) {
+    // dataflow factorisation: 1 chain CTA + kHelpers row helpers + P x Q workers, all co-resident
+    const size_t dyn2 = sizeof(double) * ((size_t)kDfTiles * kTileSm + (size_t)L.nblk * kTile);
+    if (dyn2 > 200 * 1024) return M3R_ERR_UNSUPPORTED;
+    int dev = 0;
+    M3R_CUDA_CHECK(cudaGetDevice(&dev));
+    static int cap_dev = -1, cap_ctas = 0;
+    static size_t cap_dyn = 0;
+    if (cap_dev != dev || cap_dyn != dyn2) {  // (cheap; keyed by device and dynamic shared memory)
+      int sms = 0, per_sm = 0;
+      M3R_CUDA_CHECK(cudaFuncSetAttribute(gn_solve_df_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn2));
+      M3R_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+      M3R_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gn_solve_df_kernel, kDfThreads, dyn2));
+      if (per_sm < 1) return M3R_ERR_UNSUPPORTED;
+      if (const char* e = getenv("M3R_SOLVE_CTAS_PER_SM")) per_sm = per_sm < atoi(e) ? per_sm : atoi(e);  // experiments
+      cap_ctas = sms * (per_sm > 3 ? 3 : per_sm);
+      cap_dev = dev;
+      cap_dyn = dyn2;
+    }
+    const int max_workers = cap_ctas - 1 - kHelpers;
+    if (max_workers < 1) return M3R_ERR_UNSUPPORTED;
+    int Q = 1;
+    while ((Q + 1) * (Q + 1) <= max_workers && Q + 1 <= L.nblk) Q++;
+    int P = max_workers / Q;
+    if (P > L.nblk + 1) P = L.nblk + 1;
+    a.done = P_.flags;
+    a.rdy = P_.flags + (size_t)(L.nblk + 1) * L.nblk;
+    a.ll = P_.ll;
+    a.P = P;
+    a.Q = Q;
+    int grid = 1 + kHelpers + P * Q;
+    if (grid < L.nblk && L.nblk <= cap_ctas) grid = L.nblk;  // phase C wants one CTA per tile column
+    void* args[] = {(void*)&a};
+    M3R_CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)gn_solve_df_kernel, dim3(grid), dim3(kDfThreads), args, dyn2, s));
+    return M3R_OK;
+  }
   if (dyn > 48 * 1024 - 20 * 1024) {
     M3R_CUDA_CHECK(cudaFuncSetAttribute(gn_solve_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
   }
-  if (g_coop_grid < 0) {
-    int dev = 0, sms = 0, per_sm = 0;
-    M3R_CUDA_CHECK(cudaGetDevice(&dev));
-    M3R_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  static int coop_dev = -1;
+  static size_t coop_dyn = 0;
+  int dev_now = 0;
+  M3R_CUDA_CHECK(cudaGetDevice(&dev_now));
+  if (g_coop_grid < 0 || coop_dev != dev_now || coop_dyn != dyn) {
+    int sms = 0, per_sm = 0;
+    M3R_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev_now));
     M3R_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gn_solve_kernel<true>, kSolveThreads, dyn));
     if (per_sm < 1) return M3R_ERR_UNSUPPORTED;
     // two CTAs per SM: the trailing update is bound by the latency of its tile loads, a second CTA hides some
     // of it (measured at dim 1785: 1.98 -> 1.87 ms per solve); more only makes the grid barriers dearer
     g_coop_grid = sms * (per_sm >= 2 ? 2 : 1);
+    coop_dev = dev_now;
+    coop_dyn = dyn;
   }
   int grid = g_coop_grid;
   const int max_useful = L.nblk * (L.nblk + 1) / 2 + L.nblk;
