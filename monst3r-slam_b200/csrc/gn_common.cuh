@@ -178,6 +178,22 @@ int launch_gn_track(const float* Twc, const float* Xs, const float* K, const GnL
                     const GnFrameTrack* ft = nullptr);
 int launch_gn_solve(float* Twc, const GnLayout& L, const GnPtrs& P, float delta_thresh, float* dx_out,
                     int32_t* info_out, cudaStream_t s);
+// shared-memory-resident single-CTA solve (gn_solve_resident.cu): systems of up to kResidentMaxTiles tiles
+constexpr int kResidentMaxTiles = 7;
+struct ResidentSolveArgs {
+  float* Twc;
+  const double* eb;
+  const int* ci;
+  const int* cj;
+  const int* inc_off;
+  const int* inc_list;
+  int* ctrl;
+  float* dx_out;
+  int32_t* info_out;
+  int N, dim, nblk;
+  float delta_thresh;
+};
+int launch_gn_solve_resident(const ResidentSolveArgs& a, cudaStream_t s);
 int launch_export_hs_gs(const GnLayout& L, const GnPtrs& P, float* Hs, float* gs, cudaStream_t s);
 int launch_pose_retr(float* Twc, const float* dx, int num_kf, int num_fix, cudaStream_t s);
 

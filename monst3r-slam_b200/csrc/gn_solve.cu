@@ -276,52 +276,63 @@ __device__ __forceinline__ void grid_barrier() {
   }
 }
 
-// Factor the 32x32 tile held in Ls (lower, stride 33) and invert the factor, all by WARP 0 with the
-// tile in registers (lane r owns row r of A / L, then lane c owns column c of L^-1): no block
-// barriers inside, pivots broadcast by shuffle.  Ls <- L (upper part zeroed), Li <- L^-1.
+// Factor the 32x32 tile held in Ls (lower, stride 33) and invert the factor, all by WARP 0 with the tile in registers
+// (lane r owns row r): no block barriers inside.  Ls <- L (upper part zeroed), Li <- L^-1.
+//  * factorisation: right-looking in LDL^T order; per pivot the unscaled column goes through a double-buffered 32-double
+//    shared array (1 STS + 16 broadcast LDS.128) and the chain carries one reciprocal; the square roots are applied to
+//    whole columns at the end.  Measured in isolation (tools/ubench_solve.cu, profiles/r02a_ubench_solve.log): 7.4k
+//    cycles against 12.5k for the round-1 version that broadcast the scaled column with 62 shuffles per pivot.
+//  * inverse: row r of L^-T by forward substitution from the unit vector e_r (lane = row, broadcast reads of L).
 // Returns (to every thread, through s_flag) false on a pivot <= 0.
-__device__ __forceinline__ bool tile_potrf_invert(double (*Ls)[kTile + 1], double (*Li)[kTile + 1], double* s_dinv, int* s_flag) {
+__device__ __forceinline__ bool tile_potrf_invert(double (*Ls)[kTile + 1], double (*Li)[kTile + 1], double* s_dinv, int* s_flag,
+                                                  double* s_colbuf /* 2 x 32 doubles, 16-byte aligned */) {
   const int lane = threadIdx.x;
   if (threadIdx.x < 32) {
     double a[kTile];
 #pragma unroll
     for (int c = 0; c < kTile; c++) a[c] = Ls[lane][c];
     bool bad = false;
-    double my_rinv = 1.0;
+    double my_d = 1.0;
 #pragma unroll
     for (int j = 0; j < kTile; j++) {
-      double d = __shfl_sync(0xffffffffu, a[j], j);
+      double* cb = s_colbuf + (j & 1) * kTile;
+      cb[lane] = a[j];
+      __syncwarp();
+      double d = cb[j];
       if (!(d > 0.0)) {
         bad = true;
         d = 1.0;
       }
-      const double rinv = rsqrt(d);
-      const double l = a[j] * rinv;  // lane j: sqrt(d); lanes r > j: L[r][j]
-      a[j] = l;
-      if (lane == j) my_rinv = rinv;
+      if (lane == j) my_d = d;
+      const double tj = a[j] * (1.0 / d);
 #pragma unroll
-      for (int c = j + 1; c < kTile; c++) a[c] -= l * __shfl_sync(0xffffffffu, l, c);
+      for (int c = (j + 1) & ~1; c < kTile; c += 2) {
+        const double2 v = *reinterpret_cast<const double2*>(cb + c);
+        if (c > j) a[c] -= tj * v.x;
+        a[c + 1] -= tj * v.y;
+      }
     }
-#pragma unroll
-    for (int c = 0; c < kTile; c++) Ls[lane][c] = (c <= lane) ? a[c] : 0.0;
-    s_dinv[lane] = my_rinv;
+    const double rs = rsqrt(my_d);  // 1 / L[lane][lane]
+    s_colbuf[lane] = rs;            // (lower half: last used by pivot 30, every lane is past pivot 31's barrier)
+    s_dinv[lane] = rs;
     if (lane == 0) *s_flag = bad ? 1 : 0;
     __syncwarp();
-    // column `lane` of L^-1 by forward substitution; L[r][m] is a shared-memory broadcast
+#pragma unroll
+    for (int c = 0; c < kTile; c++) Ls[lane][c] = (c <= lane) ? a[c] * s_colbuf[c] : 0.0;
+    __syncwarp();
+    // x = row `lane` of L^-T (= column `lane` of L^-1): x L^T = e_lane
     double x[kTile];
 #pragma unroll
-    for (int r = 0; r < kTile; r++) {
-      double s0 = (r == lane) ? 1.0 : 0.0, s1 = 0.0;
+    for (int c = 0; c < kTile; c++) x[c] = (c == lane) ? 1.0 : 0.0;
 #pragma unroll
-      for (int m = 0; m + 1 < r; m += 2) {
-        s0 -= Ls[r][m] * x[m];
-        s1 -= Ls[r][m + 1] * x[m + 1];
-      }
-      if (r & 1) s0 -= Ls[r][r - 1] * x[r - 1];
-      x[r] = (r < lane) ? 0.0 : (s0 + s1) * s_dinv[r];
+    for (int c = 0; c < kTile; c++) {
+      const double xc = x[c] * s_dinv[c];
+      x[c] = xc;
+#pragma unroll
+      for (int c2 = c + 1; c2 < kTile; c2++) x[c2] -= xc * Ls[c2][c];
     }
 #pragma unroll
-    for (int r = 0; r < kTile; r++) Li[r][lane] = x[r];
+    for (int c = 0; c < kTile; c++) Li[c][lane] = x[c];
   }
   __syncthreads();
   return *s_flag == 0;
@@ -338,6 +349,7 @@ gn_solve_kernel(const SolveArgs a) {
   __shared__ double sB[kTile][kTile + 1];
   __shared__ int s_flag;
   __shared__ double s_dinv[kTile];
+  __shared__ __align__(16) double s_colbuf[2 * kTile];
   __shared__ double s_red[kSolveThreads / 32];
   extern __shared__ double s_x[];  // dimP doubles (CTA 0, phase C)
 
@@ -421,7 +433,7 @@ gn_solve_kernel(const SolveArgs a) {
         sA[r][c] = (c <= r) ? __ldcg(&H[(size_t)(kb * kTile + r) * ld + kb * kTile + c]) : 0.0;
       }
       __syncthreads();
-      if (!tile_potrf_invert(sA, sB, s_dinv, &s_flag)) failed = true;  // sA = L_kk, sB = L_kk^-1 (redundant per CTA)
+      if (!tile_potrf_invert(sA, sB, s_dinv, &s_flag, s_colbuf)) failed = true;  // sA = L_kk, sB = L_kk^-1 (redundant per CTA)
       if (blockIdx.x == 0) {
         for (int t = tid; t < kTile * kTile; t += kSolveThreads) {
           const int r = t >> 5, c = t & 31;
@@ -520,7 +532,7 @@ gn_solve_kernel(const SolveArgs a) {
           sB[r + 16][c + 16] = (c <= r) ? d11 : 0.0;
         }
         __syncthreads();
-        const bool ok = tile_potrf_invert(sB, sA, s_dinv, &s_flag);  // sB = L, sA = L^-1
+        const bool ok = tile_potrf_invert(sB, sA, s_dinv, &s_flag, s_colbuf);  // sB = L, sA = L^-1
         for (int t = tid; t < kTile * kTile; t += kSolveThreads) {
           const int r = t >> 5, c = t & 31;
           a.linv[(size_t)kn * kTile * kTile + t] = sA[r][c];
@@ -1631,6 +1643,18 @@ int launch_gn_solve(float* Twc, const GnLayout& L, const GnPtrs& P_, float delta
     gn_small_solve_kernel<<<1, kSolveThreads, small_solve_smem_bytes(L.dim), s>>>(ss);
     M3R_LAUNCH_CHECK();
     return M3R_OK;
+  }
+  static const bool force_grid = [] {
+    const char* e = getenv("M3R_SOLVE");
+    return e && e[0] == 'v' && e[1] == '1';
+  }();
+  if (L.nblk <= kResidentMaxTiles && !force_grid) {
+    // up to 33 keyframes: the whole factorisation in the shared memory of one CTA (M3R_SOLVE=v1 keeps the grid kernel: A/B)
+    ResidentSolveArgs r{};
+    r.Twc = Twc; r.eb = P_.eb; r.ci = P_.ci; r.cj = P_.cj; r.inc_off = P_.inc_off; r.inc_list = P_.inc_list;
+    r.ctrl = P_.ctrl; r.dx_out = dx_out; r.info_out = info_out; r.N = L.num_kf; r.dim = L.dim; r.nblk = L.nblk;
+    r.delta_thresh = delta_thresh;
+    return launch_gn_solve_resident(r, s);
   }
   // M3R_SOLVE=df: the experimental dataflow factorisation (gn_solve_df_kernel).  Parity-green, but on B200 its chain <->
   // helper <-> worker hand-offs (0.4 us per L2 hop, 1-1.5 us per release fence) keep it at or behind the grid-step

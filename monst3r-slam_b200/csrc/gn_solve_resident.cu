@@ -1,0 +1,363 @@
+// Shared-memory-resident solve for graphs of up to 33 keyframes (system dimension <= 224 = 7 tiles of 32): the whole
+// lower triangle of H (28 tiles, 224 KB) lives in the shared memory of ONE CTA from the assemble to the last
+// substitution, so the factorisation has no grid barrier, no flag and no L2 round trip on its critical path.
+//
+// Replaces, like gn_solve_kernel, the HOST code of the reference: SparseBlock::update_lhs / update_rhs / solve with
+// Eigen::SimplicialLLT<double> (gn_kernels.cu:57-159), pose_retr_kernel (:415-453) and the norm test (:1219-1222).
+//
+// Why (B200 measurements, profiles/r02a_ubench_solve.log and r02c_*): at 7 tiles the multi-CTA kernel spends its time
+// in hand-offs -- a grid barrier costs 1.24 us, a flag hop through L2 0.4 us, a release fence 1-1.5 us -- while the
+// arithmetic is tiny (3.4 MFLOP).  One SM has 243 GFLOP/s of DMMA: the trailing updates of the whole factorisation
+// are ~15 us of one SM, the seven dependent 32x32 tile factorisations ~28 us, and nothing else has to be waited for.
+//
+// Layout: tile (i,j), j <= i, at s_dyn + tri(i,j) * 1024 doubles, row-major with stride 32 and the column index
+// XOR-swizzled by (row & 7) << 2, which makes the 8x4 fragment loads of mma.m8n8k4.f64 conflict-free without padding
+// (padding does not fit: 28 tiles are 229 376 of the 232 448 bytes a CTA can have).  The right-hand side g is carried
+// as a vector y (the row "below" the matrix), so the factorisation also yields y = L^-1 g.
+#include "gn_device.cuh"
+
+namespace m3r {
+namespace {
+
+constexpr int kResThreads = 256;
+constexpr int kResWarps = kResThreads / 32;
+constexpr int kTileEl = kTile * kTile;
+
+__device__ __forceinline__ int sw(int r, int c) { return r * kTile + (c ^ ((r & 7) << 2)); }
+__device__ __forceinline__ int tri(int i, int j) { return i * (i + 1) / 2 + j; }
+
+__device__ __forceinline__ void dmma884(double& c0, double& c1, const double a, const double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(c0), "+d"(c1)
+               : "d"(a), "d"(b));
+}
+
+// Cholesky of one tile IN PLACE by one warp (lane = row; see tile_potrf_invert in gn_solve.cu for the scheme):
+// T <- L (upper part zeroed), rinv[c] = 1 / L[c][c].  Returns true on a pivot <= 0 (or NaN).
+__device__ __forceinline__ bool potrf_inplace(double* T, double* rinv, double* col, int lane) {
+  double a[kTile];
+#pragma unroll
+  for (int c = 0; c < kTile; c += 2) {
+    const double2 v = *reinterpret_cast<const double2*>(T + sw(lane, c));
+    a[c] = v.x;
+    a[c + 1] = v.y;
+  }
+  bool bad = false;
+  double my_d = 1.0;
+#pragma unroll
+  for (int j = 0; j < kTile; j++) {
+    double* cb = col + (j & 1) * kTile;
+    cb[lane] = a[j];
+    __syncwarp();
+    double d = cb[j];
+    if (!(d > 0.0)) {
+      bad = true;
+      d = 1.0;
+    }
+    if (lane == j) my_d = d;
+    const double tj = a[j] * (1.0 / d);
+#pragma unroll
+    for (int c = (j + 1) & ~1; c < kTile; c += 2) {
+      const double2 v = *reinterpret_cast<const double2*>(cb + c);
+      if (c > j) a[c] -= tj * v.x;
+      a[c + 1] -= tj * v.y;
+    }
+  }
+  const double rs = rsqrt(my_d);
+  col[lane] = rs;  // (lower half: last used by pivot 30; every lane is past pivot 31's barrier)
+  rinv[lane] = rs;
+  __syncwarp();
+#pragma unroll
+  for (int c = 0; c < kTile; c += 2) {
+    const double2 s = *reinterpret_cast<const double2*>(col + c);
+    *reinterpret_cast<double2*>(T + sw(lane, c)) = make_double2(c <= lane ? a[c] * s.x : 0.0, c + 1 <= lane ? a[c + 1] * s.y : 0.0);
+  }
+  return bad;
+}
+
+// rows of X <- rows of X * L^-T by forward substitution (one warp, lane = row); L is a swizzled tile, read by column
+template <int C>
+__device__ __forceinline__ void trsm_step_sw(double (&x)[kTile], const double* L, const double* rinv) {
+  const double xc = x[C] * rinv[C];
+  x[C] = xc;
+#pragma unroll
+  for (int c2 = 0; c2 < kTile; c2++)
+    if (c2 > C) x[c2] -= xc * L[c2 * kTile + (C ^ ((c2 & 7) << 2))];
+  if constexpr (C + 1 < kTile) trsm_step_sw<C + 1>(x, L, rinv);
+}
+// (template recursion instead of nested `#pragma unroll`: the compiler left the inner loop rolled, which put x[] in
+// local memory -- 4x slower, profiles/r02d)
+__device__ __forceinline__ void trsm_rows_sw(double (&x)[kTile], const double* L, const double* rinv) {
+  trsm_step_sw<0>(x, L, rinv);
+}
+
+// D -= A * B^T, all three swizzled tiles, by ONE warp (16 m8n8 accumulators)
+__device__ __forceinline__ void warp_gemm_sub(double* D, const double* A, const double* B, int lane) {
+  const int g = lane >> 2, t = lane & 3;
+  double acc[4][4][2];
+#pragma unroll
+  for (int mi = 0; mi < 4; mi++)
+#pragma unroll
+    for (int ni = 0; ni < 4; ni++) acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
+#pragma unroll
+  for (int kk = 0; kk < 8; kk++) {
+    const int pc = (kk * 4 + t) ^ (g << 2);  // rows 8*mi + g: (row & 7) == g
+    double af[4], bf[4];
+#pragma unroll
+    for (int mi = 0; mi < 4; mi++) {
+      af[mi] = A[(mi * 8 + g) * kTile + pc];
+      bf[mi] = B[(mi * 8 + g) * kTile + pc];
+    }
+#pragma unroll
+    for (int mi = 0; mi < 4; mi++)
+#pragma unroll
+      for (int ni = 0; ni < 4; ni++) dmma884(acc[mi][ni][0], acc[mi][ni][1], af[mi], bf[ni]);
+  }
+#pragma unroll
+  for (int mi = 0; mi < 4; mi++)
+#pragma unroll
+    for (int ni = 0; ni < 4; ni++) {
+      double2* d = reinterpret_cast<double2*>(D + (mi * 8 + g) * kTile + ((ni * 8 + 2 * t) ^ (g << 2)));
+      double2 v = *d;
+      v.x -= acc[mi][ni][0];
+      v.y -= acc[mi][ni][1];
+      *d = v;
+    }
+}
+
+
+__global__ void __launch_bounds__(kResThreads, 1)
+gn_solve_resident_kernel(const ResidentSolveArgs a) {
+  if (a.ctrl[CTRL_DONE]) return;
+  extern __shared__ __align__(16) double s_dyn[];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int nb = a.nblk, dim = a.dim, dimP = nb * kTile, nfree = a.N - 1;
+  const int ntile = nb * (nb + 1) / 2;
+  double* Tm = s_dyn;                   // ntile tiles
+  double* y = Tm + ntile * kTileEl;     // dimP: g, then y = L^-1 g, then x
+  double* col = y + dimP;               // 2 x 32 (potrf column buffer)
+  double* rinv = col + 2 * kTile;       // 32
+  double* red = rinv + kTile;           // kResWarps
+  int* s_fail = reinterpret_cast<int*>(red + kResWarps);
+  auto tile = [&](int i, int j) -> double* { return Tm + tri(i, j) * kTileEl; };
+  auto elem = [&](int R, int C) -> double& { return Tm[tri(R >> 5, C >> 5) * kTileEl + sw(R & 31, C & 31)]; };
+
+#ifdef M3R_SOLVE_PROF
+  long long pt[8];
+  int pn = 0;
+#define RP() do { if (tid == 0) pt[pn++] = clock64(); } while (0)
+#else
+#define RP() do { } while (0)
+#endif
+  RP();
+  // ---------------------------------------------------------------- A. assemble, in shared memory
+  for (int t = tid; t < (ntile * kTileEl + dimP) / 2; t += kResThreads) reinterpret_cast<double2*>(s_dyn)[t] = make_double2(0.0, 0.0);
+  if (tid == 0) *s_fail = 0;
+  __syncthreads();
+#ifdef M3R_SOLVE_PROF
+  const long long pz = clock64();
+#endif
+  if (tid < 7 * nfree) {
+    // thread (p, r) owns row r of every 7x7 block in block row p: all poses in flight at once (<= 224 threads), incident
+    // edges in list order (deterministic, no atomics): H_pp += A_e, H_pq -= A_e (q < p).  The three dependent global
+    // reads per entry (list -> endpoint -> block) are issued eight entries at a time.
+    const int p = tid / 7, r = tid % 7;
+    double diag[7] = {0, 0, 0, 0, 0, 0, 0};
+    double gsum = 0.0;  // g[7p + r] = sum of -b_e (pose is the edge's i) / +b_e (its j)
+    const int lo = a.inc_off[p + 1], hi = a.inc_off[p + 2];
+    for (int q0 = lo; q0 < hi; q0 += 8) {
+      int ent[8], oth[8];
+      double v[8][7], bv[8];
+#pragma unroll
+      for (int u = 0; u < 8; u++) ent[u] = q0 + u < hi ? __ldg(a.inc_list + q0 + u) : -1;
+#pragma unroll
+      for (int u = 0; u < 8; u++) {
+        oth[u] = -1;
+        if (ent[u] >= 0) {
+          const int e = ent[u] >> 1;
+          oth[u] = ((ent[u] & 1) ? __ldg(a.ci + e) : __ldg(a.cj + e)) - 1;
+          const double* blk = a.eb + (size_t)e * kEdgeBlock + 7 * r;
+#pragma unroll
+          for (int cc = 0; cc < 7; cc++) v[u][cc] = __ldcg(blk + cc);
+          bv[u] = __ldcg(a.eb + (size_t)e * kEdgeBlock + 49 + r);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 8; u++)
+        if (ent[u] >= 0) {
+          gsum += (ent[u] & 1) ? bv[u] : -bv[u];
+#pragma unroll
+          for (int cc = 0; cc < 7; cc++) {
+            diag[cc] += v[u][cc];
+            if (oth[u] >= 0 && oth[u] < p) elem(7 * p + r, 7 * oth[u] + cc) -= v[u][cc];
+          }
+        }
+    }
+#pragma unroll
+    for (int cc = 0; cc < 7; cc++)
+      if (cc <= r) elem(7 * p + r, 7 * p + cc) = diag[cc];
+    y[tid] = gsum;
+  }
+  for (int R = dim + tid; R < dimP; R += kResThreads) elem(R, R) = 1.0;  // padding rows: identity
+  __syncthreads();
+
+  RP();
+  // ---------------------------------------------------------------- B. Cholesky (right-looking, look-ahead of one tile)
+  if (warp == 0 && potrf_inplace(tile(0, 0), rinv, col, lane) && lane == 0) *s_fail = 1;
+  __syncthreads();
+#ifdef M3R_SOLVE_PROF
+  long long fp[4] = {0, 0, 0, 0}, ft = clock64();
+#define FP(i) do { if (tid == 0) { const long long n_ = clock64(); fp[i] += n_ - ft; ft = n_; } } while (0)
+#else
+#define FP(i) do { } while (0)
+#endif
+  for (int k = 0; k < nb; k++) {
+    // panel: X <- X L_kk^-T for the tiles below the diagonal and for the right-hand side, one warp each
+    const double* Lkk = tile(k, k);
+    for (int task = k + 1 + warp; task <= nb; task += kResWarps) {
+      double x[kTile];
+      double* X = task < nb ? tile(task, k) : nullptr;  // task == nb: the right-hand side (every lane computes the same row)
+#pragma unroll
+      for (int c = 0; c < kTile; c += 2) {
+        const double2 v = X ? *reinterpret_cast<const double2*>(X + sw(lane, c)) : *reinterpret_cast<const double2*>(y + k * kTile + c);
+        x[c] = v.x;
+        x[c + 1] = v.y;
+      }
+      trsm_rows_sw(x, Lkk, rinv);
+      if (X) {
+#pragma unroll
+        for (int c = 0; c < kTile; c += 2) *reinterpret_cast<double2*>(X + sw(lane, c)) = make_double2(x[c], x[c + 1]);
+      } else if (lane == 0) {
+#pragma unroll
+        for (int c = 0; c < kTile; c += 2) *reinterpret_cast<double2*>(y + k * kTile + c) = make_double2(x[c], x[c + 1]);
+      }
+    }
+    __syncthreads();
+    FP(0);
+    if (k + 1 == nb) break;
+    // trailing update with column k: tiles (i,j), k < j <= i < nb, then y_j -= L_jk y_k, over all eight warps; then warp 0
+    // factors the next diagonal tile.  (A look-ahead -- warp 0 factoring while the others update -- was slower: the
+    // update's LDS / DMMA stream stretched the latency-bound 32-pivot chain from 3.9 to 6 us, more than the update
+    // itself takes: profiles/r02d.)
+    {
+      int idx = 0;
+      for (int i = k + 1; i < nb; i++)
+        for (int j = k + 1; j <= i; j++)
+          if ((idx++) % kResWarps == warp) warp_gemm_sub(tile(i, j), tile(i, k), tile(j, k), lane);
+      for (int j = k + 1; j < nb; j++)
+        if ((idx++) % kResWarps == warp) {
+          const double* Ljk = tile(j, k);
+          double acc = 0.0;
+#pragma unroll 8
+          for (int c = 0; c < kTile; c++) acc += Ljk[sw(lane, c)] * y[k * kTile + c];
+          y[j * kTile + lane] -= acc;
+        }
+    }
+    __syncthreads();
+    FP(1);
+    if (warp == 0 && potrf_inplace(tile(k + 1, k + 1), rinv, col, lane) && lane == 0) *s_fail = 1;
+    FP(2);
+    __syncthreads();
+    FP(3);
+  }
+#ifdef M3R_SOLVE_PROF
+  if (tid == 0 && a.ctrl[CTRL_ITERS] == 0)
+    printf("RESFACT: panel trsm %.1f, diag update %.1f, potrf %.1f, wait trailing %.1f us\n", fp[0] / 1965.0, fp[1] / 1965.0, fp[2] / 1965.0, fp[3] / 1965.0);
+#endif
+
+  RP();
+  // ---------------------------------------------------------------- C. back-substitution  L^T x = y (in place in y)
+  for (int j = nb - 1; j >= 0; j--) {
+    if (warp == 0) {
+      const double* Ljj = tile(j, j);
+      const double ri = 1.0 / Ljj[sw(lane, lane)];
+      double s = y[j * kTile + lane];
+#pragma unroll
+      for (int c = kTile - 1; c >= 0; c--) {
+        const double xc = __shfl_sync(0xffffffffu, s * ri, c);
+        if (lane == c) s = xc;
+        if (lane < c) s -= Ljj[sw(c, lane)] * xc;
+      }
+      y[j * kTile + lane] = s;
+    }
+    __syncthreads();
+    for (int kb = warp; kb < j; kb += kResWarps) {  // y_kb -= L_(j,kb)^T x_j
+      const double* Ljk = tile(j, kb);
+      double acc = 0.0;
+#pragma unroll 8
+      for (int r = 0; r < kTile; r++) acc += Ljk[sw(r, lane)] * y[j * kTile + r];
+      y[kb * kTile + lane] -= acc;
+    }
+    __syncthreads();
+  }
+
+  RP();
+  // ---------------------------------------------------------------- D. dx, retraction, stop test
+  const bool failed = *s_fail != 0;  // non-SPD => dx = 0 (gn_kernels.cu:147-150)
+  double ss = 0.0;
+  for (int t = tid; t < dim; t += kResThreads) {
+    const float d = failed ? 0.0f : (float)(-y[t]);
+    a.dx_out[t] = d;
+    ss += (double)d * (double)d;
+  }
+  for (int off = 16; off > 0; off >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, off);
+  if (lane == 0) red[warp] = ss;
+  __syncthreads();
+  for (int k = 1 + tid; k < a.N; k += kResThreads) {
+    float T[8], xi[7];
+#pragma unroll
+    for (int c = 0; c < 8; c++) T[c] = a.Twc[(size_t)k * 8 + c];
+#pragma unroll
+    for (int c = 0; c < 7; c++) xi[c] = failed ? 0.0f : (float)(-y[(k - 1) * 7 + c]);
+    sim3_retract(xi, T);
+#pragma unroll
+    for (int c = 0; c < 8; c++) a.Twc[(size_t)k * 8 + c] = T[c];
+  }
+  if (tid == 0) {
+    double tot = 0.0;
+    for (int w = 0; w < kResWarps; w++) tot += red[w];
+    const float nrm = (float)sqrt(tot);
+    a.ctrl[CTRL_ITERS] += 1;
+    if (failed) a.ctrl[CTRL_FAILS] += 1;
+    if (nrm < a.delta_thresh) {
+      a.ctrl[CTRL_DONE] = 1;
+      a.ctrl[CTRL_EARLY] = 1;
+    }
+    if (a.info_out) {
+      a.info_out[0] = a.ctrl[CTRL_ITERS];
+      a.info_out[1] = a.ctrl[CTRL_FAILS];
+      a.info_out[2] = a.ctrl[CTRL_EARLY];
+      a.info_out[3] = a.ctrl[CTRL_BAD];
+    }
+#ifdef M3R_SOLVE_PROF
+    if (a.ctrl[CTRL_ITERS] == 1)
+      printf("RESPROF nb %d: (zero fill %.1f) assemble %.1f, factor %.1f, backsub %.1f, tail %.1f us (at 1.965 GHz)\n", nb, (pz - pt[0]) / 1965.0, (pt[1] - pt[0]) / 1965.0,
+             (pt[2] - pt[1]) / 1965.0, (pt[3] - pt[2]) / 1965.0, (clock64() - pt[3]) / 1965.0);
+#endif
+  }
+}
+
+}  // namespace
+
+size_t gn_solve_resident_smem_bytes(int nblk) {
+  return sizeof(double) * ((size_t)(nblk * (nblk + 1) / 2) * kTileEl + (size_t)nblk * kTile + 2 * kTile + kTile + kResWarps + 2);
+}
+
+int launch_gn_solve_resident(const ResidentSolveArgs& a, cudaStream_t s) {
+  if (a.nblk < 1 || a.nblk > kResidentMaxTiles) return M3R_ERR_UNSUPPORTED;
+  const size_t dyn = gn_solve_resident_smem_bytes(a.nblk);
+  static size_t attr_set_for = 0;  // the attribute is per function (and context): raise it when a larger system shows up
+  static int attr_dev = -1;
+  int dev = 0;
+  M3R_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev != attr_dev || dyn > attr_set_for) {
+    M3R_CUDA_CHECK(cudaFuncSetAttribute(gn_solve_resident_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+    attr_set_for = dyn;
+    attr_dev = dev;
+  }
+  gn_solve_resident_kernel<<<1, kResThreads, dyn, s>>>(a);
+  M3R_LAUNCH_CHECK();
+  return M3R_OK;
+}
+
+}  // namespace m3r
