@@ -5,14 +5,16 @@ Follows mast3r_slam/tracker.py:141-154 (solve), :156-214 (opt_pose_ray_dist_sim3
 (opt_pose_calib_sim3), mast3r_slam/nonlinear_optimizer.py:5-34 (check_convergence, huber) and
 mast3r_slam/geometry.py:12-57 (point_to_ray_dist, act_Sim3), :60-105 (project_calib).
 
-Pinning.  lietorch (Sim3.inv / mul / act / retr) is a third-party CUDA extension that is not in /root/reference
-and not installed (SURVEY finding 7), so the reference tracker itself cannot run here: the Sim(3) group
-operations are restated from lietorch's published convention (data = [t, q_xyzw, s]; act(X) = s R X + t;
-retr(tau) = exp(tau) * T with tau = [translation, rotation, log-scale]) and the exponential is the one of
-oracle/cpu_oracle.cpp (`orc_pose_retr`), which IS pinned: it reproduces the reference's pose_retr_kernel bit for
-bit against the reference's CUDA build (tests/golden/gn_*.npz).  tests/test_tracker_oracle.py closes the loop:
-with the cost test disabled, this restatement must land on the pinned Gauss-Newton oracle's pose for the
-equivalent two-keyframe graph.  Status: **pinned through the GN oracle, not against lietorch itself**.
+Pinning.  **Pinned against the reference's own python** (round 2): tests/golden/tracker_{rays,calib}.npz hold inputs,
+per-iteration costs / updates, iteration counts and final poses recorded by running the reference's unmodified
+`FrameTracker.opt_pose_ray_dist_sim3 / opt_pose_calib_sim3 / solve`, `check_convergence`, `huber`, `act_Sim3`,
+`point_to_ray_dist`, `project_calib`, `constrain_points_to_ray` (tests/golden/make_golden_tracker.py imports them from
+/root/reference; float32 torch on the CPU).  Only `lietorch` -- absent from /root/reference and from the image -- is a
+stand-in there: a Sim3 container with `.data`, `inv`, `*`, `act` (textbook Sim(3) group operations) and `retr`, which
+is the oracle's host retraction `orc.pose_retr`, itself bit-pinned to the reference's `pose_retr_kernel`
+(gn_kernels.cu:299-453, lietorch's closed form).  tests/test_tracker_oracle.py checks this restatement against the
+fixtures (same iteration count, poses within 2e-5, first cost / update within 1e-4) and, independently, against the
+pinned Gauss-Newton oracle on the equivalent two-keyframe graph.
 """
 import math
 

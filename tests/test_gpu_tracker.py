@@ -136,3 +136,31 @@ def test_cholesky_failure_raises_and_unsupported_sizes_fail_loudly():
     with pytest.raises(abi.M3RError):  # another Huber threshold than the built 1.345
         pkg("tracker").PoseOptimizer(cfg={"huber": 2.0}).opt_pose_ray_dist_sim3(d["Xf"], d["Xk"], d["T_WCf"], d["T_WCk"],
                                                                               d["Q"], d["valid"])
+
+
+@pytest.mark.parametrize("kind", ["rays", "calib"])
+def test_vs_reference_python_fixture(kind):
+    """m3r_track_frame against tests/golden/tracker_{rays,calib}.npz: inputs, final poses and iteration count recorded
+    from the reference's own FrameTracker.opt_pose_* python (tests/golden/make_golden_tracker.py; float32 torch on the
+    CPU).  Same number of iterations, poses within the BASELINE pose tolerance."""
+    need_gpu()
+    import os
+    from conftest import GOLDEN
+    d = np.load(os.path.join(GOLDEN, f"tracker_{kind}.npz"))
+    t = lambda a, dt=torch.float32: torch.from_numpy(np.ascontiguousarray(a)).to("cuda", dtype=dt)
+    opt = pkg("tracker").PoseOptimizer()
+    for k in ("max_iters", "rel_error", "delta_norm", "huber", "sigma_ray", "sigma_dist", "sigma_pixel", "sigma_depth",
+              "pixel_border", "depth_eps"):
+        assert float(opt.cfg[k]) == float(d["cfg_" + k]), k  # the mirror's defaults are config/base.yaml's
+    T_WCf, T_WCk = t(d["T_WCf"]).view(1, 8), t(d["T_WCk"]).view(1, 8)
+    Q, valid = t(d["Q"]).view(-1, 1), t(d["valid"], torch.bool).view(-1, 1)
+    if kind == "rays":
+        T_new, T_rel = opt.opt_pose_ray_dist_sim3(t(d["Xf"]), t(d["Xk"]), T_WCf, T_WCk, Q, valid)
+    else:
+        T_new, T_rel = opt.opt_pose_calib_sim3(t(d["Xf_on_ray"]), t(d["Xk_on_ray"]), T_WCf, T_WCk, Q, valid, None, None,
+                                               t(d["K"]), (int(d["h"]), int(d["w"])))
+    it, fails, early, _ = (int(v) for v in opt.last_info.cpu())
+    print(kind, "iterations", it, "reference", int(d["ref_iterations"]))
+    assert it == int(d["ref_iterations"]) and fails == 0 and early == 1
+    _check(np_(T_rel), d["ref_T_CkCf"], "T_CkCf vs reference python")
+    _check(np_(T_new), d["ref_T_WCf"], "T_WCf vs reference python")
