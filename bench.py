@@ -418,13 +418,40 @@ def run_gpu(args):
     out2 = (out_host, out_host_b)
     done = [None, None]
 
+    # What goes up per step: `full` = every input of the step (the headline e2e); `frame_only` = the keyframe side stays
+    # resident on the device between frames tracked against the same keyframe -- its ray image, descriptors, points and
+    # confidences do not change (what FrameTracker effectively does, tracker.py:31-75) -- and only the frame side, the
+    # matches' initial guess and the graph slabs are uploaded.  Byte ranges of the arena, grouped by the op that waits for them.
+    def rng(k_, row=None):
+        nb_ = inp[k_].numel() * inp[k_].element_size()
+        if row is None:
+            return (offs[k_], offs[k_] + nb_)
+        per = nb_ // inp[k_].shape[0]
+        return (offs[k_] + row * per, offs[k_] + (row + 1) * per)
+
+    def merged(rs):
+        out_ = []
+        for lo_, hi_ in sorted(rs):
+            if out_ and lo_ - out_[-1][1] < 4096:
+                out_[-1] = (out_[-1][0], hi_)
+            else:
+                out_.append((lo_, hi_))
+        return out_
+
+    upload_plan = {"full": [[sp] for sp in spans],
+                   "frame_only": [merged([rng("pts"), rng("p0")]), merged([rng("D21")]),
+                                  merged([rng("Twc0"), rng("Xs", 1), rng("Cs", 1), rng("ii"), rng("jj"), rng("idx"),
+                                          rng("valid"), rng("Q")])]}
+    mode = ["full"]
+
     def upload(slot):
         ready = []
         if done[slot] is not None:
             s_up.wait_event(done[slot])  # the step that last used this buffer set has finished
         with torch.cuda.stream(s_up):
-            for lo_, hi_ in spans:
-                dev_arena2[slot][lo_:hi_].copy_(host_arena[lo_:hi_], non_blocking=True)
+            for group in upload_plan[mode[0]]:
+                for lo_, hi_ in group:
+                    dev_arena2[slot][lo_:hi_].copy_(host_arena[lo_:hi_], non_blocking=True)
                 ready.append(s_up.record_event())
         return ready
 
@@ -472,6 +499,24 @@ def run_gpu(args):
     eb.synchronize()
     barrier()
     e2e_ms = max_over_ranks(ea.elapsed_time(eb)) / K
+    full_out = {k_: v.clone() for k_, v in out2[0].items()}
+    # same loop, keyframe side resident (both device buffer sets hold it from the full uploads above)
+    mode[0] = "frame_only"
+    done[0] = done[1] = None
+    pipelined(3)
+    torch.cuda.synchronize()
+    barrier()
+    flush_l2()
+    ea2, eb2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ea2.record()
+    pipelined(K)
+    eb2.record()
+    eb2.synchronize()
+    barrier()
+    e2e_res_ms = max_over_ranks(ea2.elapsed_time(eb2)) / K
+    h2d_res = sum(hi_ - lo_ for group in upload_plan["frame_only"] for lo_, hi_ in group)
+    res_ok = bool(all(torch.equal(out2[0][k_], full_out[k_]) for k_ in full_out))
+    mode[0] = "full"
     pipe_ok = bool(torch.equal(out2[0]["Twc"], out2[1]["Twc"]) and torch.equal(out2[0]["idx"], out2[1]["idx"])
                    and torch.equal(out2[0]["Twc"], out_host["Twc"]))
     e2e = {"value": world * N_PX / (e2e_ms * 1e-3), "unit": "px/s", "ms_per_step": e2e_ms,
@@ -482,6 +527,12 @@ def run_gpu(args):
                        "inside the region: each step's inputs arrive fresh over PCIe into the other buffer set); "
                        "`latency_*` is the same loop without overlap between steps (each step timed alone, L2 flushed)",
            "results_identical_across_buffer_sets": pipe_ok,
+           "keyframe_resident": {"value": world * N_PX / (e2e_res_ms * 1e-3), "unit": "px/s", "ms_per_step": e2e_res_ms,
+                                 "h2d_bytes_per_step": h2d_res, "d2h_bytes_per_step": d2h,
+                                 "results_identical_to_full_upload": res_ok,
+                                 "what": "same pipelined loop; the keyframe's ray image, descriptors, points and confidences "
+                                         "(rays, D11, Xs[0], Cs[0]) stay on the device between frames tracked against the same "
+                                         "keyframe, every step uploads the frame side + match initialisation + graph slabs"},
            "host_numa_node": numa.node,  # pinned buffers first-touched on the GPU's node (None: sysfs does not say)
            "api": "mast3r_slam_backends.iter_proj / refine_matches / gauss_newton_rays (pybind drop-in), pinned host "
                   "buffers (one arena, three contiguous copies); H2D on a copy stream in op order, each op waits only for its own inputs, D2H on a third stream"}
