@@ -574,6 +574,12 @@ def run_gpu(args):
     if world == 1:
         ftrack = run_frame_tracker(synth, dev)
 
+    # ---- sequence-level backend frames/s (BASELINE configs[4] stand-in), one GPU ---------------------
+    sequence = None
+    if world == 1 and not args.no_sequence:
+        torch.cuda.empty_cache()
+        sequence = run_sequence(synth, ops, dev)
+
     # ---- CPU baseline on rank 0 at N=1 --------------------------------------------------------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -589,7 +595,8 @@ def run_gpu(args):
                            "parallelism": f"replicas x{world}" if world > 1 else "1 GPU"},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * K,
                 "roofline": roofline, "kernels": kern, "cpu_baseline": cpu, "global_opt": gopt.get("c3"), "global_opt_c4": gopt.get("c4"),
-                "match_pipeline": match_pipeline, "factor_graph": fgraph, "frame_tracker": ftrack}
+                "match_pipeline": match_pipeline, "factor_graph": fgraph, "frame_tracker": ftrack,
+                "sequence": sequence}
         emit(line)
     if world > 1:
         dist.destroy_process_group()
@@ -731,6 +738,128 @@ def run_global_opt(args, name, abi, synth, mdist, dev, rank, world, comm, barrie
             "poses_bit_identical_to_unsharded": identical, "poses_identical_on_all_ranks": same_on_all_ranks,
             "poses_sha1": sha, "max_abs_pose_err_vs_gt": gerr,
             "working_set": "13 B/pt/edge slabs (>= 0.6 GB per rank at c3/8) exceed the 126 MB L2; not flushed"}
+
+
+def run_sequence(synth, ops, dev, num_frames=60, kf_every=6):
+    """BASELINE configs[4] stand-in ("SLAM frames/s"): the reference's main loop (main.py:237-326) cannot be imported here
+    (lietorch, thirdparty/monst3r and the ViT weights are absent), so this strings the repo's own mirrors of its backend
+    calls over a synthetic 512x384 sequence, in the reference's order:
+        per frame    mast3r_match_asymmetric -> matching.match (tracker.py:31-37; fused op) -> valid / Q (:41-67)
+                     -> FrameTracker.opt_pose_ray_dist_sim3 (:156-214; PoseOptimizer)
+        per keyframe FactorGraph.add_factors against the previous keyframes (main.py:133, global_opt.py:31-99; symmetric
+                     matching = two fused match calls per pair) -> solve_GN_rays (main.py:142, global_opt.py:121-153)
+    The ViT is EXCLUDED: its outputs (pointmaps in the other view's frame, confidences, descriptors) are synthesised from
+    ground truth + noise, which is what the two-view network hands the backend.  A frame becomes a keyframe when the
+    reference's test fires (match fraction < match_frac_thresh, main.py:300-305) or every `kf_every` frames (added so that the
+    60-frame sequence exercises the global optimisation).  Reported: backend frames/s (wall, one sync per frame like the
+    reference's .item()), per-stage times, and the trajectory error against ground truth."""
+    import torch
+    fgm = importlib.import_module("monst3r-slam_b200.factor_graph")
+    trk = importlib.import_module("monst3r-slam_b200.tracker")
+    seq = synth.make_sequence(num_frames, H, W, fdim=FDIM, seed=1005, device=dev)
+    n = N_PX
+    gt = seq["Twc_gt"].to(dev)
+    gen = torch.Generator(device="cpu").manual_seed(7)
+
+    def in_frame_of(a, b):
+        """points of frame b expressed in frame a's coordinates (what the two-view network predicts), + noise"""
+        Tab = synth.sim3_act(synth.sim3_inv(gt[a].double()), synth.sim3_act(gt[b].double(), seq["X"][b].double()))
+        return (Tab + 1e-3 * torch.randn(n, 3, generator=gen, dtype=torch.float64).to(dev)).float().view(1, H, W, 3).contiguous()
+
+    t_vit = [0.0]  # time spent synthesising the two-view network's outputs: NOT backend time, subtracted below
+
+    def fused_match(a, b):
+        """matching.match(X_aa, X_ba, D_aa, D_ba): for every pixel of b the matching pixel of a (idx_a2b), valid mask"""
+        torch.cuda.synchronize()
+        ts = time.perf_counter()
+        X_ba = in_frame_of(a, b)
+        torch.cuda.synchronize()
+        t_vit[0] += time.perf_counter() - ts
+        return ops.match_fused(seq["X"][a].view(1, H, W, 3), X_ba, seq["D"][a].view(1, H, W, FDIM), seq["D"][b].view(1, n, FDIM))
+
+    frames = fgm.KeyframeBuffer(n, capacity=num_frames, device=dev)
+    graph = fgm.FactorGraph(frames=frames, device=dev, capacity=64)
+    opt = trk.PoseOptimizer()
+    kf_frame = []  # sequence index of every keyframe
+
+    def add_keyframe(f, T):
+        kf_frame.append(f)
+        return frames.append(seq["X"][f], seq["C"][f], T)
+
+    add_keyframe(0, gt[0])
+    T_prev = gt[0].view(1, 8).clone()
+    est = [gt[0].clone()]
+    t_track, t_kf, iters = [], [], []
+    since_kf = 0
+    torch.cuda.synchronize()
+    t_all = time.perf_counter()
+    for f in range(1, num_frames):
+        t0 = time.perf_counter()
+        v0 = t_vit[0]
+        k = len(kf_frame) - 1
+        fk = kf_frame[k]
+        idx_f2k, valid_k = fused_match(f, fk)                       # tracker.py:31-37
+        idx = idx_f2k[0]
+        Qk = torch.sqrt(seq["Q"][f][idx] * seq["Q"][fk])            # :41
+        valid_opt = valid_k[0] & (Qk > opt.cfg["Q_conf"])           # :62-67 (C_conf = 0: confidences are > 1)
+        if os.environ.get("M3R_SEQ_VERBOSE"):
+            print(f"  track {f}: valid {float(valid_opt.float().mean()):.3f} T_prev {[round(x, 4) for x in T_prev.view(8).tolist()]} "
+                  f"T_WCk {[round(x, 4) for x in frames.T_WC[k].tolist()]}", file=sys.stderr)
+        T_WCf, T_CkCf = opt.opt_pose_ray_dist_sim3(seq["X"][f][idx].contiguous(), seq["X"][fk], T_prev, frames.T_WC[k].view(1, 8),
+                                                   Qk, valid_opt)   # :85-88
+        iters.append(int(opt.last_info[0]))
+        if os.environ.get("M3R_SEQ_VERBOSE"):
+            print(f"frame {f} vs kf {k} (frame {fk}): valid {float(valid_opt.float().mean()):.3f} iters {iters[-1]} "
+                  f"|t - gt| {float((T_WCf.view(8)[:3] - gt[f, :3]).norm()):.2e}", file=sys.stderr)
+        T_prev = T_WCf.clone()
+        est.append(T_WCf.view(8).clone())
+        since_kf += 1
+        match_frac = float(valid_opt.float().mean())
+        new_kf = match_frac < 0.333 or since_kf >= kf_every        # main.py:300-305 (+ the periodic rule, see docstring)
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        t_track.append((t1 - t0 - (t_vit[0] - v0)) * 1e3)
+        v1 = t_vit[0]
+        if new_kf:
+            since_kf = 0
+            j = add_keyframe(f, T_WCf.view(8))
+            prev = list(range(max(0, j - 3), j))                    # the last keyframes
+            if j >= 5:  # retrieval stand-in (main.py:117-131): the nearest older keyframe, if the views overlap
+                dpos = (gt[kf_frame[:j - 3], :3] - gt[f, :3]).norm(dim=1)
+                if float(dpos.min()) < 0.2:
+                    prev = [int(dpos.argmin())] + prev
+            m = [[], [], [], [], [], [], [], []]
+            for i in prev:
+                fi = kf_frame[i]
+                idx_i2j, valid_j = fused_match(fi, f)               # mast3r_match_symmetric: both orders (global_opt.py:40-52)
+                idx_j2i, valid_i = fused_match(f, fi)
+                for lst, t in zip(m, (idx_i2j, idx_j2i, valid_j, valid_i, seq["Q"][fi][None], seq["Q"][f][None],
+                                      seq["Q"][f][None], seq["Q"][fi][None])):
+                    lst.append(t)
+            graph.add_factors_from_matches(prev, [j] * len(prev), tuple(torch.cat(x).contiguous() for x in m), 0.1)
+            graph.solve_GN_rays()
+            if os.environ.get("M3R_SEQ_VERBOSE"):
+                print(f"keyframe {j} (frame {f}): pairs {prev} -> edges {graph.num_edges}, |t - gt| "
+                      f"{float((frames.T_WC[j, :3] - gt[f, :3]).norm()):.2e}", file=sys.stderr)
+            T_prev = frames.T_WC[j].view(1, 8).clone()
+            torch.cuda.synchronize()
+            t_kf.append((time.perf_counter() - t1 - (t_vit[0] - v1)) * 1e3)
+    torch.cuda.synchronize()
+    wall = time.perf_counter() - t_all - t_vit[0]
+    est = torch.stack(est)
+    # Sim(3) gauge: the first pose is ground truth and keyframe 0 is fixed, so poses are directly comparable
+    terr = (est[:, :3] - gt[:, :3]).norm(dim=1)
+    kf_err = (frames.T_WC[:len(kf_frame), :3] - gt[kf_frame, :3]).norm(dim=1)
+    return {"what": "BASELINE configs[4] stand-in: reference main-loop order over a synthetic 512x384 sequence, ViT excluded "
+                    "(its outputs synthesised from ground truth + noise); fused match -> PoseOptimizer per frame, "
+                    "FactorGraph.add_factors + solve_GN_rays per keyframe",
+            "frames": num_frames, "keyframes": len(kf_frame), "graph_edges_undirected": graph.num_edges,
+            "backend_frames_per_s": (num_frames - 1) / wall, "backend_wall_s": wall, "excluded_network_synthesis_s": t_vit[0],
+            "tracking_ms_per_frame_median": statistics.median(t_track),
+            "keyframe_ms_median": statistics.median(t_kf) if t_kf else None,
+            "tracker_iterations_median": statistics.median(iters),
+            "ate_rmse_m": float(torch.sqrt((terr ** 2).mean())), "max_translation_err_m": float(terr.max()),
+            "keyframe_translation_err_after_global_opt_m": float(kf_err.max())}
 
 
 def run_frame_tracker(synth, dev):
@@ -1069,6 +1198,7 @@ def main():
     ap.add_argument("--exchange", default="auto", choices=["auto", "allreduce"],
                     help="edge-block exchange at N > 1: auto = all-gather when the partition is equal, else all-reduce")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-sequence", action="store_true")
     args = ap.parse_args()
     # stdout carries exactly ONE JSON line: anything a library prints on fd 1 meanwhile (NCCL's version banner,
     # torchrun notices) is sent to stderr, and the line is written to the real stdout at the end.

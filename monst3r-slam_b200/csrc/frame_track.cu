@@ -29,6 +29,11 @@ __device__ Sim3d load_sim3(const float* p) {
   Sim3d T;
   for (int k = 0; k < 3; k++) T.t[k] = p[k];
   for (int k = 0; k < 4; k++) T.q[k] = p[3 + k];
+  // Unit quaternion restored on entry: inv() below is the conjugate, so a norm 1 + e in the keyframe pose would come
+  // back as (1 + e)^2 in every tracked pose and compound frame after frame (seen as an exponential drift of |q| over a
+  // 60-frame sequence with 8 keyframes, bench.py --sequence).  A no-op to within one fp32 ulp for unit input.
+  const double nq = 1.0 / sqrt(T.q[0] * T.q[0] + T.q[1] * T.q[1] + T.q[2] * T.q[2] + T.q[3] * T.q[3]);
+  for (int k = 0; k < 4; k++) T.q[k] *= nq;
   T.s = p[7];
   return T;
 }

@@ -268,3 +268,46 @@ def make_graph_exact(num_kf=4, num_und_edges=5, n=768, seed=7, device="cpu", noi
     out = dict(Twc_gt=Twc_gt.float(), Twc=Twc.float().contiguous(), Xs=Xs.float().contiguous(), Cs=Cs, K=K,
                ii=ii, jj=jj, idx=idx.contiguous(), valid=valid, Q=Q, h=h, w=w)
     return {k_: (v.to(dev) if torch.is_tensor(v) else v) for k_, v in out.items()}
+
+
+# ------------------------------------------------------------------------------------- sequences
+def make_sequence(num_frames=60, h=384, w=512, fdim=24, seed=1005, device="cpu", noise=1e-3):
+    """Config 5 stand-in: a smooth camera trajectory over the height-field world of make_graph.  For every frame: its
+    ground-truth Sim(3) pose (scale 1), the canonical pointmap X [n,3] in its own camera frame (exact ray-cast + gaussian
+    noise), a per-point confidence C and matching score Q, and a 24-d descriptor map that is a fixed function of the WORLD
+    point (random Fourier features), so descriptors of the same surface point agree across frames like a trained
+    descriptor head's would.  Returns dict(Twc_gt [F,8], X [F,n,3], C [F,n,1], Q [F,n,1], D [F,n,fdim], K, h, w)."""
+    g = _gen(seed)
+    dev = torch.device(device)
+    n = h * w
+    K = intrinsics(h, w).double()
+    coef = [(0.05 + 0.05 * torch.rand(1, generator=g).item(), 0.5 + 1.5 * torch.rand(1, generator=g).item(),
+             0.5 + 1.5 * torch.rand(1, generator=g).item(), 2 * math.pi * torch.rand(1, generator=g).item())
+            for _ in range(6)]
+    v, u = torch.meshgrid(torch.arange(h, dtype=torch.float64), torch.arange(w, dtype=torch.float64), indexing="ij")
+    rays = torch.stack(((u - K[0, 2]) / K[0, 0], (v - K[1, 2]) / K[1, 1], torch.ones_like(u)), -1).view(n, 3).to(dev)
+    fa = ((torch.rand(fdim, generator=g, dtype=torch.float64) * 2 - 1) * 12.0).to(dev)
+    fb = ((torch.rand(fdim, generator=g, dtype=torch.float64) * 2 - 1) * 12.0).to(dev)
+    fc = (torch.rand(fdim, generator=g, dtype=torch.float64) * 2 * math.pi).to(dev)
+    poses, Xs, Ds = [], [], []
+    for f in range(num_frames):
+        s = f / max(num_frames - 1, 1)
+        t = torch.tensor([0.6 * math.sin(math.pi * s), 0.25 * math.sin(2 * math.pi * s), 0.1 * math.sin(3 * math.pi * s)],
+                         dtype=torch.float64)
+        ang = math.radians(8.0) * math.sin(2 * math.pi * s)
+        q = torch.tensor([0.0, math.sin(ang / 2), 0.0, math.cos(ang / 2)], dtype=torch.float64)
+        T = torch.cat((t, q, torch.ones(1, dtype=torch.float64))).to(dev)
+        d = torch.full((n, 1), 3.0, dtype=torch.float64, device=dev)
+        Rz = quat_to_R(T[3:7])[2]
+        dzdd = (rays @ Rz)[:, None]
+        for _ in range(8):
+            Xw = sim3_act(T, rays * d)
+            d = d + (_surface(coef, Xw[:, 0], Xw[:, 1]) - Xw[:, 2])[:, None] / dzdd
+        Xw = sim3_act(T, rays * d)
+        D = torch.sin(Xw[:, 0:1] * fa + Xw[:, 1:2] * fb + fc)
+        poses.append(T)
+        Xs.append((rays * d + noise * torch.randn(n, 3, generator=g, dtype=torch.float64).to(dev)).float())
+        Ds.append(F.normalize(D, dim=-1).float())
+    C = (1.0 + torch.exp(torch.randn(num_frames, n, 1, generator=g))).float().to(dev)
+    Q = torch.exp(1.0 + 0.5 * torch.randn(num_frames, n, 1, generator=g)).float().to(dev)
+    return dict(Twc_gt=torch.stack(poses).float(), X=torch.stack(Xs), C=C, Q=Q, D=torch.stack(Ds), K=K.float().to(dev), h=h, w=w)
