@@ -267,3 +267,163 @@ class FactorGraph:
                                           c["Q_conf"], c["max_iters"], c["delta_norm"])
         self._finish(pose, unique_kf_idx, in_place)
         return out
+
+
+class ShardPlan:
+    """Host bookkeeping of the RANK-SHARDED edge store (multi-GPU half): which rank owns which pair and
+    where its directed edges sit in the global edge list.  Pure python, identical on every rank by construction (every rank
+    sees the same add_factors calls and the same accept / reject decisions).
+
+      * ownership: pair number c (counted over every pair ever OFFERED) belongs to rank c mod world -- round-robin, so
+        slabs stay balanced without ever moving between ranks;
+      * global directed edge list used by a solve: rank-major -- rank 0's accepted pairs in acceptance order, then rank
+        1's, ... each pair as (i->j, j->i).  A rank's edges are therefore one contiguous range [lo, hi) of the list,
+        which is what m3r_gn_shard wants, and its local slabs are already in that order.
+    """
+
+    def __init__(self, world):
+        self.world = int(world)
+        self.offered = 0
+        self.accepted = [[] for _ in range(self.world)]  # per rank: [(i, j)] in acceptance order
+
+    def owners(self, batch):
+        own = [(self.offered + b) % self.world for b in range(batch)]
+        self.offered += batch
+        return own
+
+    def commit(self, pairs_with_owner):
+        for i, j, r in pairs_with_owner:
+            self.accepted[r].append((int(i), int(j)))
+
+    def ranges(self):
+        """[(lo, hi)] of DIRECTED edges per rank, and the total"""
+        out, lo = [], 0
+        for r in range(self.world):
+            hi = lo + 2 * len(self.accepted[r])
+            out.append((lo, hi))
+            lo = hi
+        return out, lo
+
+    def directed_lists(self):
+        ii, jj = [], []
+        for r in range(self.world):
+            for i, j in self.accepted[r]:
+                ii += [i, j]
+                jj += [j, i]
+        return ii, jj
+
+
+class ShardedFactorGraph(FactorGraph):
+    """FactorGraph whose edge slabs are sharded over the ranks of a process group (one process per GPU): `add_factors` on
+    rank r lands a pair's slabs on its OWNER only (13 B per point per directed edge: 96 % of the graph's bytes), keyframes
+    and poses are replicated, and `solve_GN_rays / _calib` is the edge-sharded solve of DESIGN.md section 4 (one exchange of
+    the fp64 edge blocks per iteration; every rank ends with bit-identical poses).  Every rank must make the same calls.
+    `comm`: the backend's NCCL communicator (dist.init_comm); `group`: the torch.distributed group used for the host-side
+    exchange of the 2 x batch integer match counts (the accept / reject rule needs them on every rank)."""
+
+    def __init__(self, frames, rank, world, comm=None, group=None, **kw):
+        super().__init__(frames, **kw)
+        self.rank, self.world, self.comm, self.group = int(rank), int(world), comm, group
+        self.plan = ShardPlan(world)
+        self._edge_cache = None
+
+    def add_factors_from_matches(self, ii, jj, matches, min_match_frac, is_reloc=False):
+        """as FactorGraph.add_factors_from_matches; `matches` holds the whole batch, the rank admits the rows it owns"""
+        idx_i2j = matches[0]
+        batch, n = idx_i2j.shape[0], idx_i2j.shape[1]
+        if self.store is None:
+            self.store = EdgeStore(self._num_pts or n, self._capacity, self.device)
+        st = self.store
+        own = self.plan.owners(batch)
+        mine = [b for b in range(batch) if own[b] == self.rank]
+        local = {}
+        if mine:
+            st.reserve(st.num_und + len(mine))
+            sel = torch.as_tensor(mine, dtype=torch.int64, device=self.device)
+            sub = tuple(t.index_select(0, sel).contiguous() for t in matches)
+            c = abi.edge_admit(*sub, float(self.cfg["Q_conf"]), st.idx, st.valid, st.Q, st.num_und).cpu().numpy()
+            local = {b: (int(c[k, 0]), int(c[k, 1])) for k, b in enumerate(mine)}
+        counts = np.zeros((batch, 2), np.int64)
+        if self.world > 1:
+            import torch.distributed as tdist
+            box = [None] * self.world
+            tdist.all_gather_object(box, local, group=self.group)
+            for d in box:
+                for b, v in d.items():
+                    counts[b] = v
+        else:
+            for b, v in local.items():
+                counts[b] = v
+        c32 = counts.astype(np.float32) / np.float32(n)
+        invalid = np.minimum(c32[:, 0], c32[:, 1]) < np.float32(min_match_frac)
+        ii_h = np.asarray([int(v) for v in ii], dtype=np.int64)
+        jj_h = np.asarray([int(v) for v in jj], dtype=np.int64)
+        invalid = (~(ii_h == (jj_h - 1))) & invalid
+        if invalid.any() and is_reloc:
+            return False
+        keep = [b for b in range(batch) if not invalid[b]]
+        base, new_local = st.num_und, 0
+        for k, b in enumerate(mine):  # compact the owned, accepted rows
+            if invalid[b]:
+                continue
+            if new_local != k:
+                st.move_slot(base + k, base + new_local)
+            rows = slice(2 * (base + new_local), 2 * (base + new_local) + 2)
+            st.ii2[rows] = torch.tensor([ii_h[b], jj_h[b]], dtype=torch.int64, device=self.device)
+            st.jj2[rows] = torch.tensor([jj_h[b], ii_h[b]], dtype=torch.int64, device=self.device)
+            new_local += 1
+        st.num_und = base + new_local
+        self.plan.commit([(ii_h[b], jj_h[b], own[b]) for b in keep])
+        for b in keep:
+            self._ids.add(int(ii_h[b]))
+            self._ids.add(int(jj_h[b]))
+        self._unique = None
+        self._edge_cache = None
+        return len(keep) > 0
+
+    @property
+    def num_edges_global(self):
+        return sum(len(a) for a in self.plan.accepted)
+
+    def _sharded_args(self):
+        from . import dist as mdist
+        if self._edge_cache is None:
+            ii, jj = self.plan.directed_lists()
+            parts, total = self.plan.ranges()
+            if any(hi == lo for lo, hi in parts):
+                raise RuntimeError("sharded solve: every rank must own at least one accepted pair")
+            self._edge_cache = (torch.as_tensor(ii, dtype=torch.int64, device=self.device),
+                                torch.as_tensor(jj, dtype=torch.int64, device=self.device), parts, total)
+        ii, jj, parts, total = self._edge_cache
+        lo, hi = parts[self.rank]
+        shard = None
+        if self.world > 1:
+            shard = mdist.make_shard(lo, hi, self.comm, mdist.exchange_for_partition(parts, total))
+        st, E2 = self.store, hi - lo
+        return ii, jj, st.idx[:E2], st.valid[:E2].unsqueeze(-1), st.Q[:E2].unsqueeze(-1), shard
+
+    def _solve(self, kind, K, img_size):
+        c = self.cfg
+        unique_kf_idx = self.get_unique_kf_idx()
+        if unique_kf_idx.numel() <= c["pin"]:
+            return None
+        Xs, T_WCs, Cs, in_place = self.get_poses_points(unique_kf_idx)
+        if kind == abi.GN_CALIB:
+            Xs = abi.constrain_points_to_ray(img_size, Xs.contiguous(), K)
+            prm = abi.make_params(abi.GN_CALIB, c["sigma_pixel"], c["sigma_depth"], c["C_conf"], c["Q_conf"], c["max_iters"],
+                                  c["delta_norm"], int(img_size[0]), int(img_size[1]), c["pixel_border"], c["depth_eps"])
+        else:
+            prm = abi.make_params(abi.GN_RAYS, c["sigma_ray"], c["sigma_dist"], c["C_conf"], c["Q_conf"], c["max_iters"],
+                                  c["delta_norm"])
+        ii, jj, idx, valid, Q, shard = self._sharded_args()
+        pose = T_WCs if in_place else T_WCs.contiguous()
+        ws, _ = abi.gn_workspace(Xs.shape[0], ii.numel(), Xs.shape[1], self.device, edges_local=idx.shape[0])
+        out = abi.gauss_newton(prm, pose, Xs.contiguous(), Cs.contiguous(), K, ii, jj, idx, valid, Q, shard=shard, workspace=ws)
+        self._finish(pose, unique_kf_idx, in_place)
+        return out
+
+    def solve_GN_rays(self):
+        return self._solve(abi.GN_RAYS, None, None)
+
+    def solve_GN_calib(self, img_size):
+        return self._solve(abi.GN_CALIB, self.K, img_size)

@@ -126,3 +126,22 @@ def test_exchange_choice_is_a_function_of_the_global_partition():
     assert mdist.exchange_for_partition([(0, 2), (2, 4), (4, 6), (6, 8)], 8) == abi.EXCHANGE_ALLGATHER
     sh = mdist.make_shard(2, 4, None, abi.EXCHANGE_ALLGATHER)
     assert (sh.edge_lo, sh.edge_hi, sh.exchange) == (2, 4, 1)
+
+
+def test_shard_plan_round_robin_and_rank_major_order():
+    """host bookkeeping of the rank-sharded edge store: ownership by offered-pair counter, contiguous rank-major ranges"""
+    import importlib
+    fgm = importlib.import_module("monst3r-slam_b200.factor_graph")
+    p = fgm.ShardPlan(3)
+    own = p.owners(4)
+    assert own == [0, 1, 2, 0]
+    p.commit([(0, 1, own[0]), (1, 2, own[1]), (2, 3, own[3])])  # pair 2 (owner 2) was rejected
+    assert p.owners(2) == [1, 2]                                   # the counter runs over OFFERED pairs
+    p.commit([(3, 4, 1), (0, 4, 2)])
+    parts, total = p.ranges()
+    assert parts == [(0, 4), (4, 8), (8, 10)] and total == 10
+    ii, jj = p.directed_lists()
+    assert ii == [0, 1, 2, 3, 1, 2, 3, 4, 0, 4] and jj == [1, 0, 3, 2, 2, 1, 4, 3, 4, 0]
+    mdist = importlib.import_module("monst3r-slam_b200.dist")
+    abi = importlib.import_module("monst3r-slam_b200.abi")
+    assert mdist.exchange_for_partition(parts, total) == abi.EXCHANGE_ALLREDUCE

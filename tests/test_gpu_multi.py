@@ -34,5 +34,8 @@ def test_two_rank_sharded_solve_bit_identical_to_unsharded():
             c = r["cases"][name]
             assert c["bit_identical_to_unsharded"] and c["identical_across_ranks"], (name, c)
             assert c["info"][:2] == [10, 0], (name, c)
+        ss = r["cases"]["sharded_store"]
+        assert ss["global_pairs"] == 90 and ss["local_pairs"] == 45 and ss["identical_across_ranks"], ss
+        assert ss["max_abs_diff_vs_single_device_graph"] < 1e-5 and ss["moved"] > 1e-3, ss
         assert r["cases"]["allgather_on_uneven_rejected"] is True
         assert r["cases"]["comm_allreduce_f64_exact"] is True
