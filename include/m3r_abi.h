@@ -66,6 +66,23 @@ int m3r_iter_proj_ws(const float* rays_img, const float* pts3d_norm, const float
                      uint8_t* converged, int b, int h, int w, int n, int max_iter, float lambda_init,
                      float cost_thresh, void* workspace, size_t workspace_bytes, void* stream);
 
+/* Same op again, for callers that may not allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  The 48-byte-per-texel
+ * re-pack scratch of m3r_iter_proj_ws lives in a file-scope `static __device__` array inside the library, sized for
+ * M3R_ITER_PROJ_STATIC_MAX_TEXELS texels (b*h*w <= 512*384 = one frame at the reference's working resolution;
+ * 9 437 184 bytes that every GPU loading the library holds until exit).  The call allocates nothing (no cudaMalloc /
+ * cudaFree, no library or torch allocation) and takes no workspace argument; results are identical to m3r_iter_proj.
+ *   - b*h*w beyond the maximum -> M3R_ERR_WORKSPACE, with the sizes in m3r_last_error(); nothing is enqueued.
+ *   - rays_img must be 16-byte aligned and p_init / p_new 8-byte aligned (M3R_ERR_BAD_ARG otherwise).
+ *   - ALL calls on a device share the one array: calls that overlap on the GPU (different streams or host threads)
+ *     race on it; serialise them on one stream.  Nothing in it needs clearing between calls (texels [0, b*h*w) are
+ *     rewritten by the call's first kernel before its second kernel reads exactly that range). */
+#define M3R_ITER_PROJ_STATIC_MAX_TEXELS (512 * 384)
+size_t m3r_iter_proj_static_max_texels(void);
+int m3r_iter_proj_static(const float* rays_img, const float* pts3d_norm, const float* p_init, float* p_new,
+                         uint8_t* converged, int b, int h, int w, int n, int max_iter, float lambda_init,
+                         float cost_thresh, void* stream);
+
 /* refine_matches: D11 [b,h,w,fdim], D21 [b,n,fdim], p1 [b,n,2] i64 (u,v) -> p1_new [b,n,2] i64.
  * The f16 variant reproduces c10::Half arithmetic (every * and + rounded to fp16, k ascending,
  * best score starts at 0); f32/f64 start at FLT_MIN/DBL_MIN like the reference template. */

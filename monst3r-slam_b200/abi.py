@@ -25,7 +25,7 @@ EXPORTS = [
     "m3r_gauss_newton", "m3r_gn_prepare", "m3r_gn_pack", "m3r_gn_accumulate", "m3r_gn_edge_blocks", "m3r_gn_solve_retract",
     "m3r_gn_export_hs_gs", "m3r_pose_retr", "m3r_comm_unique_id", "m3r_comm_init", "m3r_comm_destroy",
     "m3r_comm_allreduce_f64", "m3r_edge_admit", "m3r_constrain_points_to_ray",
-    "m3r_track_frame", "m3r_track_workspace_bytes",
+    "m3r_track_frame", "m3r_track_workspace_bytes", "m3r_iter_proj_static", "m3r_iter_proj_static_max_texels",
 ]
 
 
@@ -66,6 +66,8 @@ def _load():
     lib.m3r_gn_workspace_bytes_sharded.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int]
     lib.m3r_track_workspace_bytes.restype = C.c_size_t
     lib.m3r_track_workspace_bytes.argtypes = [C.c_int]
+    lib.m3r_iter_proj_static_max_texels.restype = C.c_size_t
+    lib.m3r_iter_proj_static_max_texels.argtypes = []
     return lib
 
 
@@ -119,6 +121,23 @@ def iter_proj(rays_img_with_grad, pts_3d_norm, p_init, max_iter, lambda_init, co
                                  _ptr(conv), b, h, w, n, int(max_iter), C.c_float(lambda_init),
                                  C.c_float(cost_thresh), _stream()), "m3r_iter_proj")
     return [p_new, conv]
+
+
+def iter_proj_static(rays_img_with_grad, pts_3d_norm, p_init, p_new, converged, max_iter, lambda_init, cost_thresh):
+    """m3r_iter_proj_static: the library's static device scratch, caller-provided outputs -- nothing is allocated, here or
+    in the library.  p_new [b,n,2] f32 and converged [b,n] bool are written in place.  Calls share the scratch: keep them
+    on one stream."""
+    for t, nm in ((rays_img_with_grad, "rays_img_with_grad"), (pts_3d_norm, "pts_3d_norm"), (p_init, "p_init"),
+                  (p_new, "p_new")):
+        _req(t, nm, torch.float32)
+    _req(converged, "converged", torch.bool)
+    b, h, w, c = rays_img_with_grad.shape
+    assert c == 9
+    n = p_init.shape[1]
+    assert tuple(p_new.shape) == (b, n, 2) and tuple(converged.shape) == (b, n)
+    _check(lib.m3r_iter_proj_static(_ptr(rays_img_with_grad), _ptr(pts_3d_norm), _ptr(p_init), _ptr(p_new), _ptr(converged),
+                                    b, h, w, n, int(max_iter), C.c_float(lambda_init), C.c_float(cost_thresh), _stream()),
+           "m3r_iter_proj_static")
 
 
 def match_fused(X11, X21, D11, D21, idx_init, max_iter, lambda_init, cost_thresh, dist_thresh, radius,

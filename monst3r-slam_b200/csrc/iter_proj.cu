@@ -19,6 +19,8 @@
 // One thread per target direction, 128-thread CTAs (4 warps), grid sized over all of b*n.
 #include <cuda_fp16.h>
 
+#include <mutex>
+
 #include "common.cuh"
 
 namespace m3r {
@@ -524,6 +526,83 @@ extern "C" int m3r_iter_proj_ws(const float* rays_img, const float* pts3d_norm, 
   cfg.numAttrs = 1;
   M3R_CUDA_CHECK(cudaLaunchKernelEx(&cfg, m3r::iter_proj_padded_kernel<false>, pad, npix, pts3d_norm, p_init, p_new,
                                     converged, h, w, n, max_iter, lambda_init, cost_thresh, m3r::IterProjPost{}));
+  return M3R_OK;
+}
+
+// ---- iter_proj with library-owned static scratch (no allocation anywhere on the call path) ---------------
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (CUDA graph capture, tight serving loops).  The re-packed ray image lives in a file-scope device array
+// of M3R_ITER_PROJ_STATIC_MAX_TEXELS texels x 48 B = 9 437 184 B, held by every GPU that loads the library until exit.
+// Every call shares the array: calls that overlap on the GPU (two streams, two host threads) RACE on it.  Nothing in
+// it has to start at zero -- the re-pack kernel rewrites texels [0, b*h*w) before the projection kernel reads exactly
+// that range -- so the last call's contents are simply overwritten.
+namespace m3r {
+namespace {
+static __device__ __align__(256) float4 g_iter_proj_scratch[(size_t)M3R_ITER_PROJ_STATIC_MAX_TEXELS * kPadF4];
+constexpr int kMaxDevices = 64;
+std::mutex g_scratch_mu;
+float4* g_scratch_ptr[kMaxDevices] = {};  // device address of the array, per device (the host-side symbol is NOT one)
+
+// set-up, once per device, with that device current
+int iter_proj_static_scratch(float4** out) {
+  int dev = -1;
+  M3R_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) {
+    set_last_error_text("m3r_iter_proj_static: device ordinal out of range");
+    return M3R_ERR_UNSUPPORTED;
+  }
+  std::lock_guard<std::mutex> lk(g_scratch_mu);
+  if (!g_scratch_ptr[dev]) {
+    float4* p = nullptr;
+    M3R_CUDA_CHECK(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_iter_proj_scratch));
+    if (!p) {
+      set_last_error_text("m3r_iter_proj_static: cudaGetSymbolAddress returned a null address");
+      return M3R_ERR_CUDA;
+    }
+    g_scratch_ptr[dev] = p;
+  }
+  *out = g_scratch_ptr[dev];
+  return M3R_OK;
+}
+}  // namespace
+}  // namespace m3r
+
+extern "C" size_t m3r_iter_proj_static_max_texels(void) { return M3R_ITER_PROJ_STATIC_MAX_TEXELS; }
+
+extern "C" int m3r_iter_proj_static(const float* rays_img, const float* pts3d_norm, const float* p_init,
+                                    float* p_new, uint8_t* converged, int b, int h, int w, int n, int max_iter,
+                                    float lambda_init, float cost_thresh, void* stream) {
+  if (!rays_img || !pts3d_norm || !p_init || !p_new || !converged) return M3R_ERR_BAD_ARG;
+  if (b < 0 || n < 0 || h < 3 || w < 3 || max_iter < 0) return M3R_ERR_BAD_ARG;
+  if (b == 0 || n == 0) return M3R_OK;
+  if (b > 65535) return M3R_ERR_BAD_ARG;
+  const size_t npix = static_cast<size_t>(b) * h * w;
+  if (npix > static_cast<size_t>(M3R_ITER_PROJ_STATIC_MAX_TEXELS)) {
+    char msg[160];
+    snprintf(msg, sizeof(msg), "m3r_iter_proj_static: b*h*w = %zu texels exceeds the static scratch of %d texels (use m3r_iter_proj_ws)",
+             npix, M3R_ITER_PROJ_STATIC_MAX_TEXELS);
+    m3r::set_last_error_text(msg);
+    return M3R_ERR_WORKSPACE;
+  }
+  if ((reinterpret_cast<uintptr_t>(rays_img) & 15) != 0 ||
+      ((reinterpret_cast<uintptr_t>(p_init) | reinterpret_cast<uintptr_t>(p_new)) & 7) != 0) {
+    m3r::set_last_error_text("m3r_iter_proj_static: rays_img must be 16-byte aligned, p_init / p_new 8-byte aligned");
+    return M3R_ERR_BAD_ARG;
+  }
+  if (max_iter == 0)  // nothing to sample: the plain kernel (no scratch at all) is the cheaper one, as in m3r_iter_proj_ws
+    return m3r_iter_proj(rays_img, pts3d_norm, p_init, p_new, converged, b, h, w, n, max_iter, lambda_init, cost_thresh, stream);
+  float4* pad = nullptr;
+  if (int rc = m3r::iter_proj_static_scratch(&pad)) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t per_cta = static_cast<size_t>(m3r::kRepackWarps) * 32;
+  m3r::iter_proj_repack_kernel<<<static_cast<unsigned>((npix + per_cta - 1) / per_cta), m3r::kRepackWarps * 32, 0, st>>>(
+      rays_img, pad, npix);
+  M3R_LAUNCH_CHECK();
+  // plain stream order between the two launches (no programmatic overlap: nothing else may touch the shared array)
+  m3r::iter_proj_padded_kernel<false><<<dim3((n + m3r::kIterProjThreads - 1) / m3r::kIterProjThreads, b),
+                                        m3r::kIterProjThreads, 0, st>>>(pad, npix, pts3d_norm, p_init, p_new, converged, h, w, n,
+                                                                        max_iter, lambda_init, cost_thresh, m3r::IterProjPost{});
+  M3R_LAUNCH_CHECK();
   return M3R_OK;
 }
 
