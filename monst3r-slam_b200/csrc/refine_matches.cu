@@ -294,6 +294,19 @@ __device__ __forceinline__ void staged_columns(const Desc& q, const unsigned cha
   }
 }
 
+#ifdef M3R_REFINE_PROF  // per-CTA timeline (tools/refine_prof.py): [cta][0..3] = t0, t1 (globaltimer ns), smid, passes;
+// [4+4*lvl ..] = cycles waiting for the box, cycles scoring, cycles in the global-gather fallback, outlier count
+__device__ long long g_refine_prof[4096 * 40];
+__device__ __forceinline__ long long gtime() {
+  long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#define RPROF(...) __VA_ARGS__
+#else
+#define RPROF(...)
+#endif
+
 __global__ void __launch_bounds__(kStThreads, M3R_REFINE_CTAS)
 refine_staged_kernel(const __half* __restrict__ D11, const __half* __restrict__ D21,
                      const int64_t* __restrict__ p1, int64_t* __restrict__ p1_new, int h, int w,
@@ -317,6 +330,8 @@ refine_staged_kernel(const __half* __restrict__ D11, const __half* __restrict__ 
     s_red[tid][4] = 0; s_red[tid][5] = 0; s_red[tid][6] = 0; s_red[tid][7] = 0;
     s_red2[tid][0] = INT_MAX; s_red2[tid][1] = INT_MIN; s_red2[tid][2] = INT_MAX; s_red2[tid][3] = INT_MIN;
   }
+  RPROF(long long* prof = g_refine_prof + (blockIdx.y * gridDim.x + blockIdx.x) * 40; long long pc0 = 0; int npass = 0;
+        if (tid == 0) { unsigned sm; asm volatile("mov.u32 %0, %smid;" : "=r"(sm)); prof[0] = gtime(); prof[2] = sm; })
   const uint32_t bar = smem_u32(&s_bar);
   if (tid == 0) {
     mbar_init(bar, 1);
@@ -391,6 +406,7 @@ refine_staged_kernel(const __half* __restrict__ D11, const __half* __restrict__ 
     const bool reuse = reuse_ok && res && have_box && bh > 0 && max(umin - rd, 0) >= res_px0 && min(umax + rd, w - 1) <= res_px1 &&
                        py0 >= res_py0 && py1 <= res_py1;
     if (reuse) {
+      RPROF(pc0 = clock64();)
       const bool interior = u0 - rd >= 0 && u0 + rd < w && v0 - rd >= 0 && v0 + rd < h;
       const bool fast = __all_sync(0xffffffffu, !inl || interior);
       if (inl) {
@@ -406,6 +422,7 @@ refine_staged_kernel(const __half* __restrict__ D11, const __half* __restrict__ 
           vb = v0 - rd + (bc & 7) * d;
         }
       }
+      RPROF(__syncthreads(); if (tid == 0) prof[5 + 4 * lvl] += clock64() - pc0;)
     } else
     // ---- passes over groups of u-offset columns -------------------------------------------------
     if (have_box && bh > 0) {
@@ -429,8 +446,10 @@ refine_staged_kernel(const __half* __restrict__ D11, const __half* __restrict__ 
           for (int r = tid; r < bh; r += kStThreads)
             bulk_g2s(smem_u32(sbox) + r * pitch * kPxBytes,
                      img + (static_cast<size_t>(py0 + r) * w + px0) * kPxBytes, rowbytes, bar, pol);
+          RPROF(pc0 = clock64(); npass++;)
           mbar_wait(bar, phase);
           phase ^= 1u;
+          RPROF(if (tid == 0) prof[4 + 4 * lvl] += clock64() - pc0; pc0 = clock64();)
           if (i0 == 0 && c == kStCnt) {  // the whole window of this level is resident now
             res = true;
             res_px0 = px0; res_px1 = px1; res_py0 = py0; res_py1 = py1; res_pitch = pitch;
@@ -450,16 +469,20 @@ refine_staged_kernel(const __half* __restrict__ D11, const __half* __restrict__ 
               vb = v0 - rd + (bc & 7) * d;
             }
           }
+          RPROF(__syncthreads(); if (tid == 0) prof[5 + 4 * lvl] += clock64() - pc0;)
         }
         i0 += c;
       }
     }
+    RPROF(pc0 = clock64(); { const int no = __syncthreads_count(valid && !inl); if (tid == 0) prof[7 + 4 * lvl] = no; })
     if (valid && !inl) gather_level(img, q, u0, v0, d, kStRadius, w, h, best, ub, vb);
+    RPROF(__syncthreads(); if (tid == 0) prof[6 + 4 * lvl] += clock64() - pc0;)
     u0 = ub;
     v0 = vb;
   }
   const bool same = ub == static_cast<int>(p.x) && vb == static_cast<int>(p.y);
   if (valid) reinterpret_cast<longlong2*>(p1_new)[qi] = same ? p : make_longlong2(ub, vb);
+  RPROF(if (tid == 0) { prof[1] = gtime(); prof[3] = npass; })
 }
 
 // ---- generic path: any fdim, fp16 / fp32 / fp64, one candidate at a time ----------------------
@@ -549,6 +572,19 @@ int check_args(const void* D11, const void* D21, const void* p1, const void* p1_
 
 }  // namespace
 }  // namespace m3r
+
+#ifdef M3R_REFINE_PROF  // debugging export of the -DM3R_REFINE_PROF build only (tools/refine_prof.py)
+extern "C" int m3r_debug_refine_prof(long long* host_out, int clear) {
+  if (clear) {
+    void* p = nullptr;
+    M3R_CUDA_CHECK(cudaGetSymbolAddress(&p, m3r::g_refine_prof));
+    M3R_CUDA_CHECK(cudaMemset(p, 0, sizeof(m3r::g_refine_prof)));
+    return M3R_OK;
+  }
+  M3R_CUDA_CHECK(cudaMemcpyFromSymbol(host_out, m3r::g_refine_prof, sizeof(m3r::g_refine_prof)));
+  return M3R_OK;
+}
+#endif
 
 extern "C" int m3r_refine_matches_f16(const void* D11, const void* D21, const int64_t* p1,
                                       int64_t* p1_new, int b, int h, int w, int n, int fdim,
