@@ -235,17 +235,26 @@ gn_solve_resident_kernel(const ResidentSolveArgs a) {
     __syncthreads();
     FP(0);
     if (k + 1 == nb) break;
-    // trailing update with column k: tiles (i,j), k < j <= i < nb, then y_j -= L_jk y_k, over all eight warps; then warp 0
-    // factors the next diagonal tile.  (A look-ahead -- warp 0 factoring while the others update -- was slower: the
-    // update's LDS / DMMA stream stretched the latency-bound 32-pivot chain from 3.9 to 6 us, more than the update
-    // itself takes: profiles/r02d.)
-    {
-      int idx = 0;
+    // trailing update with column k (tiles (i,j), k < j <= i < nb, and y_j -= L_jk y_k) with a look-ahead of one tile:
+    // warp 1 updates the next diagonal tile first and hands it to warp 0 over named barrier 1; warp 0 factors it while
+    // warps 1-7 run the rest of the update.  Same box, tools/ab_solve.py 32,120: 140-141 us per iteration against
+    // 149.6 us with the factorisation after the update (profiles/r02d).
+    if (warp == 0) {
+      asm volatile("bar.sync 1, 64;" ::: "memory");
+      if (potrf_inplace(tile(k + 1, k + 1), rinv, col, lane) && lane == 0) *s_fail = 1;
+    } else {
+      if (warp == 1) {
+        warp_gemm_sub(tile(k + 1, k + 1), tile(k + 1, k), tile(k + 1, k), lane);
+        asm volatile("bar.sync 1, 64;" ::: "memory");
+      }
+      int idx = 1;  // (warp 1 starts one task late: it has done the diagonal tile)
       for (int i = k + 1; i < nb; i++)
-        for (int j = k + 1; j <= i; j++)
-          if ((idx++) % kResWarps == warp) warp_gemm_sub(tile(i, j), tile(i, k), tile(j, k), lane);
+        for (int j = k + 1; j <= i; j++) {
+          if (i == k + 1) continue;  // (k+1, k+1): done above
+          if ((idx++) % (kResWarps - 1) == warp - 1) warp_gemm_sub(tile(i, j), tile(i, k), tile(j, k), lane);
+        }
       for (int j = k + 1; j < nb; j++)
-        if ((idx++) % kResWarps == warp) {
+        if ((idx++) % (kResWarps - 1) == warp - 1) {
           const double* Ljk = tile(j, k);
           double acc = 0.0;
 #pragma unroll 8
@@ -253,16 +262,13 @@ gn_solve_resident_kernel(const ResidentSolveArgs a) {
           y[j * kTile + lane] -= acc;
         }
     }
-    __syncthreads();
     FP(1);
-    if (warp == 0 && potrf_inplace(tile(k + 1, k + 1), rinv, col, lane) && lane == 0) *s_fail = 1;
-    FP(2);
     __syncthreads();
     FP(3);
   }
 #ifdef M3R_SOLVE_PROF
   if (tid == 0 && a.ctrl[CTRL_ITERS] == 0)
-    printf("RESFACT: panel trsm %.1f, diag update %.1f, potrf %.1f, wait trailing %.1f us\n", fp[0] / 1965.0, fp[1] / 1965.0, fp[2] / 1965.0, fp[3] / 1965.0);
+    printf("RESFACT: panel trsm %.1f, look-ahead potrf (warp 0) %.1f, wait for the update %.1f us\n", fp[0] / 1965.0, fp[1] / 1965.0, fp[3] / 1965.0);
 #endif
 
   RP();
