@@ -143,7 +143,8 @@ extern "C" int m3r_track_frame(float* T_WCf, float* T_CkCf_out, const float* T_W
 
   track_init_kernel<<<1, 32, 0, s>>>(T_WCk, T_WCf, Twc2, ii, jj);
   M3R_LAUNCH_CHECK();
-  int rc = launch_gn_prepare(ii, jj, L, P, s, dx_out, kPose, info_out);  // also zeroes dx_out / info_out
+  const unsigned ll_epoch = gn_next_epoch();
+  int rc = launch_gn_prepare(ii, jj, L, P, s, dx_out, kPose, info_out, ll_epoch);  // also zeroes dx_out / info_out
   if (rc != M3R_OK) return rc;
   rc = launch_gn_pack(nullptr, nullptr, valid, Q, L, P, prm, 0, 1, s);
   if (rc != M3R_OK) return rc;
@@ -155,7 +156,7 @@ extern "C" int m3r_track_frame(float* T_WCf, float* T_CkCf_out, const float* T_W
   fuse.enabled = 1;
   GnFrameTrack ft{Xk, Xf, p->rel_error};
   int launched = 0;
-  rc = launch_gn_track(Twc2, nullptr, K, L, P, prm, fuse, &launched, s, &ft);
+  rc = launch_gn_track(Twc2, nullptr, K, L, P, prm, fuse, &launched, s, &ft, ll_epoch);
   if (rc != M3R_OK) return rc;
   if (!launched) {
     set_last_error_text("m3r_track_frame: the persistent kernel cannot hold this frame (num_pts % 8 != 0, Xf not "

@@ -637,7 +637,7 @@ __device__ unsigned long long g_dbg[1024];
 #define TRK(slot) do { } while (0)
 #endif
 constexpr int kTrackThreads = 512;
-constexpr int kTrackMaxEdges = 8;
+// (kTrackMaxEdges = 8: gn_common.cuh)
 constexpr int kTrackPtBytes = 34;  // Xs[j] 12 | record 8 | local index 2 | gathered Xs[i][m] 12
 constexpr int kTrackMaxPts = 4800; // x 34 B = 163 KB staged + 33 KB solve + 33 KB static <= 227 KB per CTA
 
@@ -1240,13 +1240,14 @@ int launch_gn_accumulate(const float* Twc, const float* Xs, const float* K, cons
 // Whole GN loop in one cooperative launch (gn_track_kernel).  *launched = 0 when the problem is not
 // tracking-sized (the caller then runs the per-iteration path).
 int launch_gn_track(const float* Twc, const float* Xs, const float* K, const GnLayout& L, const GnPtrs& P,
-                    const m3r_gn_params& prm, const GnFuse& fuse, int* launched, cudaStream_t s, const GnFrameTrack* ft) {
+                    const m3r_gn_params& prm, const GnFuse& fuse, int* launched, cudaStream_t s, const GnFrameTrack* ft,
+                    unsigned ll_epoch) {
   *launched = 0;
   if (ft && L.num_edges != 1) return M3R_ERR_BAD_ARG;
   const int E = L.num_edges;
   if (!fuse.enabled || E < 1 || E > kTrackMaxEdges || L.dim > kSmallDim || prm.max_iter < 1) return M3R_OK;
-  static int num_sms = 0, coop = 0;
-  if (num_sms == 0) {
+  int num_sms = 0, coop = 0;  // (per call: two attribute reads are cheaper than a cache that goes stale across devices)
+  {
     int dev = 0;
     M3R_CUDA_CHECK(cudaGetDevice(&dev));
     M3R_CUDA_CHECK(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
@@ -1276,8 +1277,10 @@ int launch_gn_track(const float* Twc, const float* Xs, const float* K, const GnL
   // (gn_layout reserves >= (4 * 148 + 8) x kAcc doubles)
   // (+ two buffers of grid x 16 B of cost partials in frame-tracker mode)
   if ((size_t)4 * E * ta.cpe + 32 > std::max((size_t)E * a.chunks, (size_t)4 * kNumSMs + 32)) return M3R_OK;
-  static std::atomic<unsigned> g_epoch{1};
-  ta.epoch = g_epoch.fetch_add(1) & 0xfffffu;
+  // per-launch nonce in the flag tag, drawn by the caller before gn_prepare (which clears this workspace's flag words
+  // on first use and whenever the 20-bit nonce has wrapped since: gn_common.cuh)
+  if (ll_epoch == 0) return M3R_ERR_BAD_ARG;
+  ta.epoch = ll_epoch & 0xfffffu;
   const size_t dyn_track = (size_t)ta.stage_pts * kTrackPtBytes + small_solve_smem_bytes(L.dim);
   if (ft) {
     switch (prm.kind) {

@@ -16,7 +16,8 @@ constexpr int kAccumThreads = 256;
 constexpr int kSolveThreads = 256;
 
 // ctrl words (device int32)
-enum { CTRL_DONE = 0, CTRL_ITERS = 1, CTRL_FAILS = 2, CTRL_EARLY = 3, CTRL_BAD = 4, CTRL_FAIL_NOW = 5, CTRL_WORDS = 16 };
+enum { CTRL_DONE = 0, CTRL_ITERS = 1, CTRL_FAILS = 2, CTRL_EARLY = 3, CTRL_BAD = 4, CTRL_FAIL_NOW = 5, CTRL_LL_GEN = 15, CTRL_WORDS = 16 };
+// (CTRL_LL_GEN survives gn_prepare: generation under which the tracking kernel's flag words were last cleared)
 
 // Point-chunking of one edge: a pure function of (E, n) with E the FULL edge count, so that the
 // workspace size, every launch and every shard of a multi-GPU run agree (a shard's edge blocks are
@@ -28,6 +29,7 @@ enum { CTRL_DONE = 0, CTRL_ITERS = 1, CTRL_FAILS = 2, CTRL_EARLY = 3, CTRL_BAD =
 constexpr int kAccumCtasPerSM = 3;
 constexpr int kMaxChunkPts = 3072;  // x 22 B (Xs[j] 12 + record 8 + local index 2) = 66 KB of smem per CTA
 constexpr int kSmallDim = 63;       // systems up to 9 free poses are solved inside the accumulate kernel
+constexpr int kTrackMaxEdges = 8;   // directed edges the persistent tracking kernel takes
 struct GnChunking {
   int chunk_pts, chunks;
 };
@@ -160,8 +162,12 @@ struct GnFuse {
 };
 
 // entry points implemented in gn_accum.cu / gn_solve.cu (host launchers)
+// ll_epoch: nonce of the persistent tracking kernel's flag words for the solve that follows (gn_next_epoch(); 0 = no such
+// kernel will run on this workspace).  The prepare kernel clears the flag words whenever the workspace was last
+// cleared under another generation (epoch >> 20) of the 20-bit nonce, i.e. on first use and once per wrap.
+unsigned gn_next_epoch();
 int launch_gn_prepare(const int64_t* ii, const int64_t* jj, const GnLayout& L, const GnPtrs& P, cudaStream_t s,
-                      float* zero_dx = nullptr, int n_dx = 0, int32_t* zero_info = nullptr);
+                      float* zero_dx = nullptr, int n_dx = 0, int32_t* zero_info = nullptr, unsigned ll_epoch = 0);
 int launch_gn_pack(const float* Cs, const int64_t* idx, const uint8_t* valid, const float* Q, const GnLayout& L,
                    const GnPtrs& P, const m3r_gn_params& prm, int e_lo, int e_hi, cudaStream_t s);
 int launch_gn_accumulate(const float* Twc, const float* Xs, const float* K, const GnLayout& L, const GnPtrs& P,
@@ -175,7 +181,7 @@ struct GnFrameTrack {
 };
 int launch_gn_track(const float* Twc, const float* Xs, const float* K, const GnLayout& L, const GnPtrs& P,
                     const m3r_gn_params& prm, const GnFuse& fuse, int* launched, cudaStream_t s,
-                    const GnFrameTrack* ft = nullptr);
+                    const GnFrameTrack* ft = nullptr, unsigned ll_epoch = 0);
 int launch_gn_solve(float* Twc, const GnLayout& L, const GnPtrs& P, float delta_thresh, float* dx_out,
                     int32_t* info_out, cudaStream_t s);
 // shared-memory-resident single-CTA solve (gn_solve_resident.cu): systems of up to kResidentMaxTiles tiles

@@ -269,7 +269,8 @@ extern "C" int m3r_gauss_newton(float* Twc, const float* Xs, const float* Cs, co
   GnFuse fuse{};
   fuse.Twc = Twc; fuse.dx_out = dx_out; fuse.info_out = info_out; fuse.delta_thresh = params->delta_thresh;
   fuse.enabled = (L.dim <= kSmallDim) && !(shard && shard->comm) && lo == 0 && hi == num_edges;
-  rc = launch_gn_prepare(ii, jj, L, P, s, dx_out, kPose * (num_kf - 1), info_out);  // also zeroes dx_out / info_out
+  const unsigned ll_epoch = (params->max_iter > 0 && fuse.enabled) ? gn_next_epoch() : 0u;
+  rc = launch_gn_prepare(ii, jj, L, P, s, dx_out, kPose * (num_kf - 1), info_out, ll_epoch);  // also zeroes dx_out / info_out
   if (rc != M3R_OK) return rc;
   if (params->max_iter > 0) {
     rc = launch_gn_pack(Cs, idx, valid, Q, L, P, *params, lo, hi, s);
@@ -278,7 +279,7 @@ extern "C" int m3r_gauss_newton(float* Twc, const float* Xs, const float* Cs, co
   if (params->max_iter > 0 && fuse.enabled) {
     // tracking-sized: the whole loop is one cooperative launch (gn_track_kernel)
     int launched = 0;
-    rc = launch_gn_track(Twc, Xs, K, L, P, *params, fuse, &launched, s);
+    rc = launch_gn_track(Twc, Xs, K, L, P, *params, fuse, &launched, s, nullptr, ll_epoch);
     if (rc != M3R_OK) return rc;
     if (launched) return M3R_OK;
   }

@@ -23,6 +23,8 @@
 
 #include <cstdlib>
 
+#include <atomic>
+
 #include "gn_device.cuh"
 
 namespace cg = cooperative_groups;
@@ -37,7 +39,8 @@ gn_prepare_kernel(const int64_t* __restrict__ ii, const int64_t* __restrict__ jj
                   int* __restrict__ ci, int* __restrict__ cj, unsigned* __restrict__ bitmap,
                   unsigned* __restrict__ prefix, int* __restrict__ inc_off, int* __restrict__ inc_list,
                   int* __restrict__ order, unsigned* __restrict__ counters, int* __restrict__ ctrl,
-                  float* __restrict__ zero_dx, int n_dx, int32_t* __restrict__ zero_info) {
+                  float* __restrict__ zero_dx, int n_dx, int32_t* __restrict__ zero_info,
+                  uint4* __restrict__ zero_ll, int n_ll16, int ll_gen) {
   // presence bitmap over [id_min, id_max] only: keyframe ids are a few hundred apart at most, so the
   // scan touches a handful of words instead of the whole M3R_MAX_KF_ID range
   const int tid = threadIdx.x, nt = blockDim.x;
@@ -50,12 +53,21 @@ gn_prepare_kernel(const int64_t* __restrict__ ii, const int64_t* __restrict__ jj
     s_max = -1;
   }
   for (int k = tid; k <= E; k += nt) counters[k] = 0u;
-  if (tid < CTRL_WORDS) ctrl[tid] = 0;
+  const bool clear_ll = n_ll16 > 0 && ctrl[CTRL_LL_GEN] != ll_gen;  // (every thread reads before anyone writes: barrier below)
+  __syncthreads();
+  if (tid < CTRL_WORDS && tid != CTRL_LL_GEN) ctrl[tid] = 0;
+  if (clear_ll && tid == 0) ctrl[CTRL_LL_GEN] = ll_gen;
   // outputs of the solve that follows start from zero (max_iter == 0, or a solve that never runs): folded in
   // here instead of two cudaMemsetAsync launches in front of every Gauss-Newton call
   if (zero_dx)
     for (int k = tid; k < n_dx; k += nt) zero_dx[k] = 0.f;
   if (zero_info && tid < 4) zero_info[tid] = 0;
+  // The persistent tracking kernel's flag words ({tag | payload}, gn_accum.cu) live in caller memory that is never
+  // initialised and outlives the launch; the tag carries a 20-bit launch nonce.  They are cleared (tag 0 is never
+  // waited for) when this workspace is first used and whenever the nonce has wrapped since the last clear, so a stale
+  // word can never carry the tag a later launch waits for.
+  if (clear_ll)
+    for (int k = tid; k < n_ll16; k += nt) zero_ll[k] = make_uint4(0u, 0u, 0u, 0u);
   if (2 * E <= 32 && N <= 32) {
     // Small graphs (tracking: 2 edges): everything in warp 0 with shuffles, no block barrier, no pass through global
     // memory — same outputs as the general path below (which costs ~10 us of barriers for a two-edge graph).
@@ -1619,10 +1631,23 @@ int g_coop_grid = -1;  // CTAs that can be co-resident for the cooperative varia
 
 }  // namespace
 
+unsigned gn_next_epoch() {
+  static std::atomic<unsigned> g_epoch{1u << 20};  // generation (epoch >> 20) starts at 1: never the 0 of a zeroed header
+  unsigned e = g_epoch.fetch_add(1);
+  if (e == 0) e = g_epoch.fetch_add(1);  // (0 means "no tracking kernel")
+  return e;
+}
+
 int launch_gn_prepare(const int64_t* ii, const int64_t* jj, const GnLayout& L, const GnPtrs& P, cudaStream_t s,
-                      float* zero_dx, int n_dx, int32_t* zero_info) {
+                      float* zero_dx, int n_dx, int32_t* zero_info, unsigned ll_epoch) {
+  // tracking-sized graphs may run in the persistent kernel: clear its flag words (two gather buffers of <= kNumSMs x
+  // kAcc x 16 B, 192 pose words, two buffers of <= kNumSMs x 16 B cost words: 172 032 B at the start of P.partials)
+  int n_ll16 = 0;
+  if (ll_epoch != 0 && L.num_edges <= kTrackMaxEdges && L.dim <= kSmallDim)
+    n_ll16 = (2 * kNumSMs * kAcc * 16 + 192 * 8 + 2 * kNumSMs * 16) / 16;
   gn_prepare_kernel<<<1, 1024, 0, s>>>(ii, jj, L.num_edges, L.num_kf, P.ci, P.cj, P.bitmap, P.prefix,
-                                       P.inc_off, P.inc_list, P.order, P.counters, P.ctrl, zero_dx, n_dx, zero_info);
+                                       P.inc_off, P.inc_list, P.order, P.counters, P.ctrl, zero_dx, n_dx, zero_info,
+                                       reinterpret_cast<uint4*>(P.partials), n_ll16, static_cast<int>(ll_epoch >> 20) + 1);
   M3R_LAUNCH_CHECK();
   return M3R_OK;
 }
