@@ -17,7 +17,7 @@ LIB = os.path.join(HERE, os.environ.get("M3R_LIB_DIR", "lib"))  # M3R_LIB_DIR: s
 INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 
 CU_SOURCES = ["iter_proj.cu", "refine_matches.cu", "gn_accum.cu", "gn_solve.cu", "gn_solve_resident.cu", "gn_driver.cu", "edge_store.cu", "frame_track.cu"]
-HEADERS = ["common.cuh", "gn_common.cuh", "tma.cuh", "gn_device.cuh"]
+HEADERS = ["common.cuh", "gn_common.cuh", "tma.cuh", "gn_device.cuh", "gn_tile.cuh"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--expt-relaxed-constexpr"]
 NVCC_FLAGS += os.environ.get("M3R_NVCC_EXTRA", "").split()  # e.g. -DM3R_TRACK_PROF for tools/track_prof.py (then rebuild with force)

@@ -25,7 +25,7 @@
 
 #include <atomic>
 
-#include "gn_device.cuh"
+#include "gn_tile.cuh"
 
 namespace cg = cooperative_groups;
 
@@ -277,7 +277,21 @@ struct SolveArgs {
   int* rdy;
   unsigned long long* ll;
   int P, Q;
+  int pipe_off;  // gn_solve_kernel: offset (doubles) of the trailing update's cp.async tile pipeline in dynamic smem; 0 = none
 };
+
+// ---- pieces of the pipelined trailing update (gn_solve_kernel, B2) ------------------------------------------------
+#ifndef M3R_UPD_STAGES
+#define M3R_UPD_STAGES 3
+#endif
+constexpr int kUpdStages = M3R_UPD_STAGES;          // tiles in flight per CTA (24 KB each)
+constexpr int kUpdStageDoubles = 3 * kTile * kTile; // L_Ik, L_Jk and the destination tile A_IJ
+__device__ __forceinline__ void cp_async16(double* smem_dst, const double* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 template <bool COOP>
 __device__ __forceinline__ void grid_barrier() {
@@ -351,10 +365,17 @@ __device__ __forceinline__ bool tile_potrf_invert(double (*Ls)[kTile + 1], doubl
 }
 
 // measured (tools/solve_prof.py): dim 1785 (56 tiles) 1.90 -> 1.66 ms with the look-ahead, dim 217 (7 tiles) 139 -> 160 us
-constexpr int kLookaheadMinTiles = 12;
+constexpr int kLookaheadMinTiles = 8;
 
+// One CTA per SM (round 2): the one-warp substitution / factorisation of the v2 chain keep a tile row in registers
+// (64 + operands); at the 128 registers of two CTAs per SM they spilled (508 B) and the solve ran at 990 us, at 255
+// registers it runs at 796 us (profiles/r02s).  The trailing update hides its L2 latency with cp.async instead of a
+// second resident CTA.
+#ifndef M3R_SOLVE_MINCTAS
+#define M3R_SOLVE_MINCTAS 1
+#endif
 template <bool COOP>
-__global__ void __launch_bounds__(kSolveThreads, 2)
+__global__ void __launch_bounds__(kSolveThreads, M3R_SOLVE_MINCTAS)
 gn_solve_kernel(const SolveArgs a) {
   if (a.ctrl[CTRL_DONE]) return;  // uniform over the grid: set only by a previous launch
   __shared__ double sA[kTile][kTile + 1];
@@ -437,7 +458,110 @@ gn_solve_kernel(const SolveArgs a) {
   const int diag_cta = (int)gridDim.x - 1;
   const bool is_diag = lookahead && (int)blockIdx.x == diag_cta;
   const int n_work = lookahead ? (int)gridDim.x - 1 : (int)gridDim.x;  // CTAs that share the bulk work
+  // v2 (round 2) of the look-ahead path: no tile inverse on the chain.  The diagonal CTA factors tile (kb+1, kb+1) with
+  // the LDL-ordered one-warp potrf of gn_tile.cuh (3.9 us instead of 7 for potrf + inverse), its symmetric update is 16
+  // DMMA per warp on swizzled shared-memory tiles with the destination tile prefetched before the barrier, and every
+  // panel tile is solved by forward substitution against L_kk (one warp, the tile's rows in registers) instead of a
+  // product with L_kk^-1.  The inverses the back-substitution wants are formed afterwards, all tiles in parallel.
+  const bool v2 = lookahead && a.pipe_off > 0;
+  const int lane = tid & 31, wrp = tid >> 5;
+  double* const pipe = s_x + a.pipe_off;
+  double* Lcur = pipe;                      // L_kk, swizzled (diagonal CTA: alternates with Dnext)
+  double* Dnext = pipe + 2 * kTileEl;       // diagonal CTA: tile (kb+1, kb+1) being updated / factored
+  double* const Xs = pipe + kTileEl;        // diagonal CTA: L_(kb+1, kb)
+  double* const colb = pipe + 3 * kTileEl;  // potrf column buffer (2 x 32), then 1 / diag (32)
+  double* const rinv = colb + 2 * kTile;
+  // one warp: rows of panel tile (I, kb) <- rows * L_kk^-T, lane = row; optionally also into a swizzled smem tile
+  auto load_rows = [&](double (&x)[kTile], int I, int kb_) {
+    const double* row = &H[(size_t)(I * kTile + lane) * ld + kb_ * kTile];
+#pragma unroll
+    for (int c = 0; c < kTile; c += 2) {
+      const double2 v = __ldcg(reinterpret_cast<const double2*>(row + c));
+      x[c] = v.x;
+      x[c + 1] = v.y;
+    }
+  };
+  auto trsm_loaded = [&](double (&x)[kTile], int I, int kb_, const double* Ltile, double* smem_out) {
+    double* row = &H[(size_t)(I * kTile + lane) * ld + kb_ * kTile];
+    trsm_rows_sw(x, Ltile, rinv);
+#pragma unroll
+    for (int c = 0; c < kTile; c += 2) {
+      *reinterpret_cast<double2*>(row + c) = make_double2(x[c], x[c + 1]);
+      if (smem_out) *reinterpret_cast<double2*>(smem_out + sw(lane, c)) = make_double2(x[c], x[c + 1]);
+    }
+  };
+  auto trsm_tile = [&](int I, int kb_, const double* Ltile, double* smem_out) {
+    double x[kTile];
+    load_rows(x, I, kb_);
+    trsm_rows_sw(x, Ltile, rinv);
+    double* row = &H[(size_t)(I * kTile + lane) * ld + kb_ * kTile];
+#pragma unroll
+    for (int c = 0; c < kTile; c += 2) {
+      *reinterpret_cast<double2*>(row + c) = make_double2(x[c], x[c + 1]);
+      if (smem_out) *reinterpret_cast<double2*>(smem_out + sw(lane, c)) = make_double2(x[c], x[c + 1]);
+    }
+  };
   for (int kb = 0; kb < nblk; kb++) {
+    if (v2) {
+      // B1 (v2): L_kk into shared memory, substitution on this CTA's panel tile
+      if (kb == 0) {
+        for (int t = tid; t < kTileEl; t += kSolveThreads) {
+          const int r = t >> 5, c = t & 31;
+          Lcur[sw(r, c)] = (c <= r) ? __ldcg(&H[(size_t)r * ld + c]) : 0.0;
+        }
+        __syncthreads();
+        if (wrp == 0) {
+          const bool bad = potrf_inplace(Lcur, rinv, colb, lane);  // redundant per CTA: no barrier before the first panel
+          if (lane == 0) s_flag = bad ? 1 : 0;
+        }
+        __syncthreads();
+        if (s_flag) failed = true;
+        if (blockIdx.x == 0) {
+          for (int t = tid; t < kTileEl; t += kSolveThreads) {
+            const int r = t >> 5, c = t & 31;
+            const double v = Lcur[sw(r, c)];
+            a.linv[t] = v;
+            if (c <= r) H[(size_t)r * ld + c] = v;
+          }
+        }
+      } else if (!is_diag) {
+        // this CTA's (first) panel tile travels together with L_kk: one exposed L2 round trip instead of two
+        const int I0 = kb + 1 + ((kb + 1 < nblk) ? 1 : 0) + blockIdx.x;
+        double x0[kTile];
+        if (wrp == 0 && I0 <= nblk) load_rows(x0, I0, kb);
+        __syncthreads();
+        for (int t = tid; t < kTileEl; t += kSolveThreads) Lcur[sw(t >> 5, t & 31)] = __ldcg(&a.linv[(size_t)kb * kTileEl + t]);
+        if (__ldcg(&a.ctrl[CTRL_FAIL_NOW])) failed = true;
+        __syncthreads();
+        if (tid < kTile) rinv[tid] = 1.0 / Lcur[sw(tid, tid)];
+        __syncthreads();
+        SLV(0);
+        if (wrp == 0) {
+          if (I0 <= nblk) trsm_loaded(x0, I0, kb, Lcur, nullptr);
+          for (int I = I0 + n_work; I <= nblk; I += n_work) trsm_tile(I, kb, Lcur, nullptr);
+        }
+      }  // (the diagonal CTA holds L_kk and 1 / diag from its own factorisation)
+      if (kb == 0 || is_diag) SLV(0);
+      const int kn = kb + 1;
+      if (is_diag) {
+        if (kn < nblk) {
+          if (wrp == 0) {
+            trsm_tile(kn, kb, Lcur, Xs);
+          } else {  // meanwhile: the tile the chain updates next (final since the previous step's update)
+            for (int e = tid - 32; e < kTileEl / 2; e += kSolveThreads - 32) {
+              const int r = e >> 4, c2 = (e & 15) * 2;
+              *reinterpret_cast<double2*>(Dnext + sw(r, c2)) =
+                  __ldcg(reinterpret_cast<const double2*>(&H[(size_t)(kn * kTile + r) * ld + kn * kTile + c2]));
+            }
+          }
+        }
+      } else if (wrp == 0 && kb == 0) {
+        for (int I = kb + 1 + ((kn < nblk) ? 1 : 0) + blockIdx.x; I <= nblk; I += n_work) trsm_tile(I, kb, Lcur, nullptr);
+      }
+      SLV(1);
+      grid_barrier<COOP>();
+      SLV(2);
+    } else {
     // B1: diagonal tile, inverse, TRSM on this CTA's panel tiles
     if (kb == 0 || !lookahead) {
       for (int t = tid; t < kTile * kTile; t += kSolveThreads) {
@@ -512,11 +636,54 @@ gn_solve_kernel(const SolveArgs a) {
     SLV(1);
     grid_barrier<COOP>();
     SLV(2);
+    }  // (!v2)
     // B2: trailing update  A_IJ -= L_Ik * L_Jk^T  for kb < J <= I <= nblk (J < nblk)
     const int rem = nblk - kb;          // tile rows below kb, including the rhs row
     const int ncols = rem - 1;          // tile columns kb+1 .. nblk-1
     // tiles enumerated row by row: row i (1..rem) has min(i, ncols) tiles
     const int ntiles = ncols * (ncols + 1) / 2 + ncols;  // triangle + rhs row
+    if (v2 && is_diag && kb + 1 < nblk) {
+      const int kn = kb + 1;
+      __syncthreads();  // Xs (warp 0) and Dnext (warps 1-7) are complete
+      {
+        const int g = lane >> 2, t4 = lane & 3, mi = wrp >> 1, ni0 = (wrp & 1) * 2;
+        double acc[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
+#pragma unroll
+        for (int kk = 0; kk < 8; kk++) {
+          const int pc = (kk * 4 + t4) ^ (g << 2);
+          const double av = Xs[(mi * 8 + g) * kTile + pc];
+          dmma884(acc[0][0], acc[0][1], av, Xs[(ni0 * 8 + g) * kTile + pc]);
+          dmma884(acc[1][0], acc[1][1], av, Xs[((ni0 + 1) * 8 + g) * kTile + pc]);
+        }
+#pragma unroll
+        for (int n2 = 0; n2 < 2; n2++) {
+          double2* d = reinterpret_cast<double2*>(Dnext + (mi * 8 + g) * kTile + (((ni0 + n2) * 8 + 2 * t4) ^ (g << 2)));
+          double2 v = *d;
+          v.x -= acc[n2][0];
+          v.y -= acc[n2][1];
+          *d = v;
+        }
+      }
+      __syncthreads();
+      if (wrp == 0) {
+        const bool bad = potrf_inplace(Dnext, rinv, colb, lane);
+        if (lane == 0) s_flag = bad ? 1 : 0;
+      }
+      __syncthreads();
+      for (int t = tid; t < kTileEl; t += kSolveThreads) {
+        const int r = t >> 5, c = t & 31;
+        const double v = Dnext[sw(r, c)];
+        a.linv[(size_t)kn * kTileEl + t] = v;  // L_(kn,kn) for the other CTAs' substitutions (inverted after the loop)
+        if (c <= r) H[(size_t)(kn * kTile + r) * ld + kn * kTile + c] = v;
+      }
+      if (s_flag) {
+        failed = true;
+        if (tid == 0) a.ctrl[CTRL_FAIL_NOW] = 1;
+      }
+      double* tmp = Lcur;
+      Lcur = Dnext;
+      Dnext = tmp;
+    } else
     if (is_diag && kb + 1 < nblk) {
       // while the other CTAs run the trailing update: diagonal tile (kb+1, kb+1) -= X X^T (X is still in sA),
       // factor + invert it and publish L^-1 for the next step
@@ -561,6 +728,77 @@ gn_solve_kernel(const SolveArgs a) {
     // with look-ahead tile 0 = (kb+1, kb+1) is updated (and factored) by the diagonal CTA
     const int t_first = lookahead ? (is_diag ? ntiles : 1 + (int)blockIdx.x) : (int)blockIdx.x;
     const int t_step = n_work;
+    if (a.pipe_off > 0) {
+      // Pipelined update (round 2): the three tiles of an update travel global -> shared memory by cp.async (L2 only,
+      // like __ldcg) kUpdStages tiles ahead, so their L2 round trips overlap the products of the tiles before them
+      // instead of being exposed once per tile; the product is 16 DMMA (mma.m8n8k4.f64) per warp on swizzled tiles
+      // instead of 128 DFMA per thread fed by four shared-memory loads each.  Was 3.7 us per tile (profiles/r02s).
+      double* pipe = s_x + a.pipe_off;
+      const int nmine = t_first < ntiles ? (ntiles - t_first + t_step - 1) / t_step : 0;
+      auto decode = [&](int t0, int& I, int& J) {
+        int i, j;
+        if (t0 < ncols * (ncols + 1) / 2) {
+          i = (int)((sqrt(8.0 * (double)t0 + 1.0) - 1.0) * 0.5);
+          while ((i + 1) * (i + 2) / 2 <= t0) i++;
+          while (i * (i + 1) / 2 > t0) i--;
+          j = t0 - i * (i + 1) / 2;
+        } else {
+          i = ncols;  // rhs row
+          j = t0 - ncols * (ncols + 1) / 2;
+        }
+        I = kb + 1 + i;
+        J = kb + 1 + j;
+      };
+      auto issue = [&](int n) {
+        if (n < nmine) {
+          int I, J;
+          decode(t_first + n * t_step, I, J);
+          double* st = pipe + (n % kUpdStages) * kUpdStageDoubles;
+#pragma unroll
+          for (int q = 0; q < 2; q++) {
+            const int e = tid + q * kSolveThreads, row = e >> 4, c2 = (e & 15) * 2;
+            const int so = sw(row, c2);
+            cp_async16(st + so, &H[(size_t)(I * kTile + row) * ld + kb * kTile + c2]);
+            cp_async16(st + kTile * kTile + so, &H[(size_t)(J * kTile + row) * ld + kb * kTile + c2]);
+            cp_async16(st + 2 * kTile * kTile + so, &H[(size_t)(I * kTile + row) * ld + J * kTile + c2]);
+          }
+        }
+        cp_async_commit();  // (an empty group keeps the group count uniform)
+      };
+      for (int n = 0; n < kUpdStages - 1; n++) issue(n);
+      const int lane = tid & 31, wrp = tid >> 5, g = lane >> 2, t4 = lane & 3;
+      const int mi = wrp >> 1, ni0 = (wrp & 1) * 2;
+      for (int n = 0; n < nmine; n++) {
+        issue(n + kUpdStages - 1);
+        cp_async_wait<kUpdStages - 1>();
+        __syncthreads();
+        int I, J;
+        decode(t_first + n * t_step, I, J);
+        const double* sa = pipe + (n % kUpdStages) * kUpdStageDoubles;
+        const double* sb = sa + kTile * kTile;
+        const double* sd = sb + kTile * kTile;
+        double acc[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
+#pragma unroll
+        for (int kk = 0; kk < 8; kk++) {
+          const int pc = (kk * 4 + t4) ^ (g << 2);  // rows 8*m + g: (row & 7) == g
+          const double av = sa[(mi * 8 + g) * kTile + pc];
+          const double b0 = sb[(ni0 * 8 + g) * kTile + pc], b1 = sb[((ni0 + 1) * 8 + g) * kTile + pc];
+          dmma884(acc[0][0], acc[0][1], av, b0);
+          dmma884(acc[1][0], acc[1][1], av, b1);
+        }
+        const int row = mi * 8 + g;
+#pragma unroll
+        for (int n2 = 0; n2 < 2; n2++) {
+          const int col = (ni0 + n2) * 8 + 2 * t4;
+          double2 d = *reinterpret_cast<const double2*>(sd + row * kTile + (col ^ (g << 2)));
+          d.x -= acc[n2][0];
+          d.y -= acc[n2][1];
+          *reinterpret_cast<double2*>(&H[(size_t)(I * kTile + row) * ld + J * kTile + col]) = d;
+        }
+        __syncthreads();  // the stage is refilled by the next iteration's issue
+      }
+      cp_async_wait<0>();
+    } else
     for (int t0 = t_first; t0 < ntiles; t0 += t_step) {
       int i, j;
       if (t0 < ncols * (ncols + 1) / 2) {
@@ -602,6 +840,29 @@ gn_solve_kernel(const SolveArgs a) {
     SLV(3);
     grid_barrier<COOP>();
     SLV(4);
+  }
+  if (v2) {
+    // the back-substitution multiplies by L_kk^-1: invert the diagonal tiles now, one per CTA, lane j = column j by
+    // forward substitution (a.linv holds L_kk until here)
+    for (int kb2 = blockIdx.x; kb2 < nblk; kb2 += gridDim.x) {
+      __syncthreads();
+      for (int t = tid; t < kTileEl; t += kSolveThreads) pipe[sw(t >> 5, t & 31)] = __ldcg(&a.linv[(size_t)kb2 * kTileEl + t]);
+      __syncthreads();
+      if (tid < kTile) rinv[tid] = 1.0 / pipe[sw(tid, tid)];
+      __syncthreads();
+      if (wrp == 0) {
+        double x[kTile];
+#pragma unroll
+        for (int i = 0; i < kTile; i++) {
+          double sacc = (i == lane) ? 1.0 : 0.0;
+#pragma unroll
+          for (int m = 0; m < i; m++) sacc -= pipe[sw(i, m)] * x[m];
+          x[i] = sacc * rinv[i];
+          a.linv[(size_t)kb2 * kTileEl + i * kTile + lane] = x[i];
+        }
+      }
+    }
+    grid_barrier<COOP>();
   }
   // ---------------------------------------------------------------- C. back-substitution  L^T x = y
   const bool par_back = COOP && nblk >= 2 && nblk <= (int)gridDim.x;
@@ -1658,8 +1919,8 @@ int launch_gn_solve(float* Twc, const GnLayout& L, const GnPtrs& P_, float delta
   a.Twc = Twc; a.eb = P_.eb; a.ci = P_.ci; a.cj = P_.cj; a.inc_off = P_.inc_off; a.inc_list = P_.inc_list;
   a.hd = P_.hd; a.linv = P_.linv; a.ctrl = P_.ctrl; a.dx_out = dx_out; a.info_out = info_out;
   a.N = L.num_kf; a.dim = L.dim; a.nblk = L.nblk; a.ld = L.ld; a.delta_thresh = delta_thresh;
-  const size_t dyn = sizeof(double) * (size_t)L.nblk * kTile;
-  if (dyn > 160 * 1024) return M3R_ERR_UNSUPPORTED;  // > 20k unknowns: out of scope for a dense solve
+  size_t dyn = sizeof(double) * (size_t)L.nblk * kTile;
+  if (dyn > 128 * 1024) return M3R_ERR_UNSUPPORTED;  // > 16k unknowns: out of scope for a dense solve
   if (L.dim <= kSmallDim) {
     SmallSolveArgs ss{};
     ss.Twc = Twc; ss.eb = P_.eb; ss.ci = P_.ci; ss.cj = P_.cj; ss.inc_off = P_.inc_off; ss.inc_list = P_.inc_list;
@@ -1723,6 +1984,15 @@ int launch_gn_solve(float* Twc, const GnLayout& L, const GnPtrs& P_, float delta
     void* args[] = {(void*)&a};
     M3R_CUDA_CHECK(cudaLaunchCooperativeKernel((const void*)gn_solve_df_kernel, dim3(grid), dim3(kDfThreads), args, dyn2, s));
     return M3R_OK;
+  }
+  static const bool no_pipe = getenv("M3R_SOLVE_NOPIPE") != nullptr;  // A/B knob: the round-1 trailing update
+  if (L.nblk >= kLookaheadMinTiles && !no_pipe) {
+    const int off = (L.nblk * kTile + 1) & ~1;  // 16-byte aligned behind s_x
+    const size_t dyn_pipe = sizeof(double) * ((size_t)off + (size_t)kUpdStages * kUpdStageDoubles);
+    if (dyn_pipe <= 200 * 1024) {  // (beyond ~7000 unknowns the round-1 path runs)
+      a.pipe_off = off;
+      dyn = dyn_pipe;
+    }
   }
   if (dyn > 48 * 1024 - 20 * 1024) {
     M3R_CUDA_CHECK(cudaFuncSetAttribute(gn_solve_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));

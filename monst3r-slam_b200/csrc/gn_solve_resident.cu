@@ -14,117 +14,13 @@
 // XOR-swizzled by (row & 7) << 2, which makes the 8x4 fragment loads of mma.m8n8k4.f64 conflict-free without padding
 // (padding does not fit: 28 tiles are 229 376 of the 232 448 bytes a CTA can have).  The right-hand side g is carried
 // as a vector y (the row "below" the matrix), so the factorisation also yields y = L^-1 g.
-#include "gn_device.cuh"
+#include "gn_tile.cuh"
 
 namespace m3r {
 namespace {
 
 constexpr int kResThreads = 256;
 constexpr int kResWarps = kResThreads / 32;
-constexpr int kTileEl = kTile * kTile;
-
-__device__ __forceinline__ int sw(int r, int c) { return r * kTile + (c ^ ((r & 7) << 2)); }
-__device__ __forceinline__ int tri(int i, int j) { return i * (i + 1) / 2 + j; }
-
-__device__ __forceinline__ void dmma884(double& c0, double& c1, const double a, const double b) {
-  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
-               : "+d"(c0), "+d"(c1)
-               : "d"(a), "d"(b));
-}
-
-// Cholesky of one tile IN PLACE by one warp (lane = row; see tile_potrf_invert in gn_solve.cu for the scheme):
-// T <- L (upper part zeroed), rinv[c] = 1 / L[c][c].  Returns true on a pivot <= 0 (or NaN).
-__device__ __forceinline__ bool potrf_inplace(double* T, double* rinv, double* col, int lane) {
-  double a[kTile];
-#pragma unroll
-  for (int c = 0; c < kTile; c += 2) {
-    const double2 v = *reinterpret_cast<const double2*>(T + sw(lane, c));
-    a[c] = v.x;
-    a[c + 1] = v.y;
-  }
-  bool bad = false;
-  double my_d = 1.0;
-#pragma unroll
-  for (int j = 0; j < kTile; j++) {
-    double* cb = col + (j & 1) * kTile;
-    cb[lane] = a[j];
-    __syncwarp();
-    double d = cb[j];
-    if (!(d > 0.0)) {
-      bad = true;
-      d = 1.0;
-    }
-    if (lane == j) my_d = d;
-    const double tj = a[j] * (1.0 / d);
-#pragma unroll
-    for (int c = (j + 1) & ~1; c < kTile; c += 2) {
-      const double2 v = *reinterpret_cast<const double2*>(cb + c);
-      if (c > j) a[c] -= tj * v.x;
-      a[c + 1] -= tj * v.y;
-    }
-  }
-  const double rs = rsqrt(my_d);
-  col[lane] = rs;  // (lower half: last used by pivot 30; every lane is past pivot 31's barrier)
-  rinv[lane] = rs;
-  __syncwarp();
-#pragma unroll
-  for (int c = 0; c < kTile; c += 2) {
-    const double2 s = *reinterpret_cast<const double2*>(col + c);
-    *reinterpret_cast<double2*>(T + sw(lane, c)) = make_double2(c <= lane ? a[c] * s.x : 0.0, c + 1 <= lane ? a[c + 1] * s.y : 0.0);
-  }
-  return bad;
-}
-
-// rows of X <- rows of X * L^-T by forward substitution (one warp, lane = row); L is a swizzled tile, read by column
-template <int C>
-__device__ __forceinline__ void trsm_step_sw(double (&x)[kTile], const double* L, const double* rinv) {
-  const double xc = x[C] * rinv[C];
-  x[C] = xc;
-#pragma unroll
-  for (int c2 = 0; c2 < kTile; c2++)
-    if (c2 > C) x[c2] -= xc * L[c2 * kTile + (C ^ ((c2 & 7) << 2))];
-  if constexpr (C + 1 < kTile) trsm_step_sw<C + 1>(x, L, rinv);
-}
-// (template recursion instead of nested `#pragma unroll`: the compiler left the inner loop rolled, which put x[] in
-// local memory -- 4x slower, profiles/r02d)
-__device__ __forceinline__ void trsm_rows_sw(double (&x)[kTile], const double* L, const double* rinv) {
-  trsm_step_sw<0>(x, L, rinv);
-}
-
-// D -= A * B^T, all three swizzled tiles, by ONE warp (16 m8n8 accumulators)
-__device__ __forceinline__ void warp_gemm_sub(double* D, const double* A, const double* B, int lane) {
-  const int g = lane >> 2, t = lane & 3;
-  double acc[4][4][2];
-#pragma unroll
-  for (int mi = 0; mi < 4; mi++)
-#pragma unroll
-    for (int ni = 0; ni < 4; ni++) acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
-#pragma unroll
-  for (int kk = 0; kk < 8; kk++) {
-    const int pc = (kk * 4 + t) ^ (g << 2);  // rows 8*mi + g: (row & 7) == g
-    double af[4], bf[4];
-#pragma unroll
-    for (int mi = 0; mi < 4; mi++) {
-      af[mi] = A[(mi * 8 + g) * kTile + pc];
-      bf[mi] = B[(mi * 8 + g) * kTile + pc];
-    }
-#pragma unroll
-    for (int mi = 0; mi < 4; mi++)
-#pragma unroll
-      for (int ni = 0; ni < 4; ni++) dmma884(acc[mi][ni][0], acc[mi][ni][1], af[mi], bf[ni]);
-  }
-#pragma unroll
-  for (int mi = 0; mi < 4; mi++)
-#pragma unroll
-    for (int ni = 0; ni < 4; ni++) {
-      double2* d = reinterpret_cast<double2*>(D + (mi * 8 + g) * kTile + ((ni * 8 + 2 * t) ^ (g << 2)));
-      double2 v = *d;
-      v.x -= acc[mi][ni][0];
-      v.y -= acc[mi][ni][1];
-      *d = v;
-    }
-}
-
 
 __global__ void __launch_bounds__(kResThreads, 1)
 gn_solve_resident_kernel(const ResidentSolveArgs a) {
