@@ -12,11 +12,16 @@
 //                 triangle and adds the incident edge blocks in edge order (deterministic, no atomics)
 //                 H_pp += A_e, H_pq -= A_e (q < p), g_p -+= b_e.  g is stored as one extra row
 //                 below H, so the factorisation also produces y = L^-1 g (bordered-matrix trick).
-//   B. Cholesky   right-looking, 32x32 tiles, fp64: every CTA factors the diagonal tile redundantly
-//                 in shared memory (no broadcast needed), inverts it, and does TRSM on its share of
-//                 the panel as a tile GEMM with L_kk^-1; grid.sync; trailing SYRK/GEMM update tiles
-//                 spread over all CTAs; grid.sync.
-//   C. back-substitution  L^T x = y by CTA 0 with the stored L_kk^-1 tiles, column-parallel.
+//   B. Cholesky   right-looking, 32x32 tiles, fp64, two grid barriers per tile step.  From 8 tiles on (the "v2"
+//                 step, round 2) one dedicated CTA walks the serial chain -- substitution on panel tile (k+1,k),
+//                 DMMA symmetric update and one-warp LDL-ordered potrf of tile (k+1,k+1) while the others update
+//                 the trailing matrix -- every other panel tile is solved by forward substitution against L_kk
+//                 (one warp, rows in registers) and the trailing update streams its three tiles per product
+//                 through a cp.async ring into DMMA (mma.m8n8k4.f64).  Below 8 tiles (and on the round-1 fallback
+//                 path) every CTA factors + inverts the diagonal tile redundantly and the panel is a tile GEMM
+//                 with L_kk^-1.  Systems of up to 7 tiles never get here: gn_solve_resident.cu.
+//   C. back-substitution  L^T x = y as a barrier-free column-block dataflow over the CTAs with the L_kk^-1 tiles
+//                 (v2 forms them after the factorisation, all tiles in parallel).
 //   D. dx = -x (0 if a pivot was <= 0: gn_kernels.cu:142-150), retraction T <- Exp(dx) T in fp32
 //      following :299-413, ||dx|| stop test, next-iteration bookkeeping.
 #include <cooperative_groups.h>
