@@ -282,6 +282,8 @@ struct SolveArgs {
   int* rdy;
   unsigned long long* ll;
   int P, Q;
+  int v4;        // gn_solve_kernel: one barrier per tile step (panel tiles formed inside the update with L_kk^-1)
+  double* ybuf;  // v4: y = L^-1 g, one block per step
   int pipe_off;  // gn_solve_kernel: offset (doubles) of the trailing update's cp.async tile pipeline in dynamic smem; 0 = none
 };
 
@@ -469,6 +471,7 @@ gn_solve_kernel(const SolveArgs a) {
   // panel tile is solved by forward substitution against L_kk (one warp, the tile's rows in registers) instead of a
   // product with L_kk^-1.  The inverses the back-substitution wants are formed afterwards, all tiles in parallel.
   const bool v2 = lookahead && a.pipe_off > 0;
+  const bool v4 = v2 && a.v4 != 0 && nblk <= (int)gridDim.x;  // (the back-substitution of v4 wants one CTA per tile column)
   const int lane = tid & 31, wrp = tid >> 5;
   double* const pipe = s_x + a.pipe_off;
   double* Lcur = pipe;                      // L_kk, swizzled (diagonal CTA: alternates with Dnext)
@@ -506,6 +509,260 @@ gn_solve_kernel(const SolveArgs a) {
       if (smem_out) *reinterpret_cast<double2*>(smem_out + sw(lane, c)) = make_double2(x[c], x[c + 1]);
     }
   };
+  if (v4) {
+    // ---- v4: ONE grid barrier per tile step -----------------------------------------------------------------------
+    // The panel phase is gone: a CTA that updates tile (I,J) with column kb forms the two panel tiles it needs itself,
+    // L_Ik = A_Ik L_kk^-T and L_Jk = A_Jk L_kk^-T, as DMMA products with the inverse of the diagonal tile (L_Ik is
+    // reused along a row of its contiguous chunk of tiles).  The raw panel tiles are never overwritten -- concurrent
+    // CTAs read them -- so the final L_Ik goes to the mirror slot (kb, I) in the unused upper triangle of H (written
+    // by the CTA that owns the first tile of row I) and y_kb to ybuf.  The chain CTA meanwhile forms L_(kb+1,kb),
+    // updates + factors + inverts tile (kb+1, kb+1) and publishes L^-1 for the next step.
+#ifdef M3R_TRACK_PROF
+    long long cpt[6] = {0, 0, 0, 0, 0, 0}, cp0 = 0;
+#define CPS() do { cp0 = clock64(); } while (0)
+#define CPT(i) do { const long long n_ = clock64(); cpt[i] += n_ - cp0; cp0 = n_; } while (0)
+#else
+#define CPS() do { } while (0)
+#define CPT(i) do { } while (0)
+#endif
+    double* const LinvS = pipe + kUpdStages * kUpdStageDoubles;   // L_kk^-1, swizzled
+    double* const XI = LinvS + kTileEl;                           // L_Ik of the current row
+    double* const XJ = XI + kTileEl;                              // L_Jk
+    double* const colb4 = XJ + kTileEl;                           // chain: potrf column buffer (64) + 1/diag (32)
+    double* const rinv4 = colb4 + 2 * kTile;
+    const int g = lane >> 2, t4 = lane & 3, mi = wrp >> 1, ni0 = (wrp & 1) * 2;
+    auto g2s = [&](double* dst, const double* src, int ldsrc) {  // 32 x 32 tile -> swizzled smem, all threads
+      for (int e = tid; e < kTileEl / 2; e += kSolveThreads) {
+        const int r = e >> 4, c2 = (e & 15) * 2;
+        *reinterpret_cast<double2*>(dst + sw(r, c2)) = __ldcg(reinterpret_cast<const double2*>(src + (size_t)r * ldsrc + c2));
+      }
+    };
+    auto s2g = [&](double* dst, int lddst, const double* src) {  // swizzled smem tile -> global, all threads
+      for (int e = tid; e < kTileEl / 2; e += kSolveThreads) {
+        const int r = e >> 4, c2 = (e & 15) * 2;
+        *reinterpret_cast<double2*>(dst + (size_t)r * lddst + c2) = *reinterpret_cast<const double2*>(src + sw(r, c2));
+      }
+    };
+    // OUT (=|-=) A B^T on swizzled smem tiles, 8 warps x two 8x8 blocks
+    auto cta_gemm = [&](double* OUT, const double* A, const double* B, bool subtract) {
+      double acc[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
+#pragma unroll
+      for (int kk = 0; kk < 8; kk++) {
+        const int pc = (kk * 4 + t4) ^ (g << 2);
+        const double av = A[(mi * 8 + g) * kTile + pc];
+        dmma884(acc[0][0], acc[0][1], av, B[(ni0 * 8 + g) * kTile + pc]);
+        dmma884(acc[1][0], acc[1][1], av, B[((ni0 + 1) * 8 + g) * kTile + pc]);
+      }
+#pragma unroll
+      for (int n2 = 0; n2 < 2; n2++) {
+        double2* d = reinterpret_cast<double2*>(OUT + (mi * 8 + g) * kTile + (((ni0 + n2) * 8 + 2 * t4) ^ (g << 2)));
+        if (subtract) {
+          double2 v = *d;
+          v.x -= acc[n2][0];
+          v.y -= acc[n2][1];
+          *d = v;
+        } else {
+          *d = make_double2(acc[n2][0], acc[n2][1]);
+        }
+      }
+    };
+    // chain CTA: factor the tile in D (swizzled), write L to H(kk,kk), invert into LinvS, publish a.linv[kk]
+    auto factor_invert_publish = [&](double* D, int kk) {
+      if (wrp == 0) {
+        const bool bad = potrf_inplace(D, rinv4, colb4, lane);
+        if (lane == 0) s_flag = bad ? 1 : 0;
+      }
+      __syncthreads();
+      CPT(2);
+      for (int t = tid; t < kTileEl; t += kSolveThreads) {
+        const int r = t >> 5, c = t & 31;
+        if (c <= r) H[(size_t)(kk * kTile + r) * ld + kk * kTile + c] = D[sw(r, c)];
+      }
+      // L^-1 by 16 x 16 blocks, L = [A 0; C B]:  [A^-1 0; -B^-1 C A^-1  B^-1].  Warps 0 and 1 invert A and B side by
+      // side (lane j < 16 = column j, forward substitution, four partial sums), then all threads form the lower-left
+      // block with two 16^3 products.  (One warp doing the whole tile took 2.5 us of the chain's 8.7 us per step.)
+      if (wrp < 2 && lane < 16) {
+        const int o = wrp * 16;
+        double x[16];
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+          double s4[4] = {(i == lane) ? 1.0 : 0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+          for (int m = 0; m < i; m++) s4[m & 3] -= D[sw(o + i, o + m)] * x[m];
+          x[i] = ((s4[0] + s4[1]) + (s4[2] + s4[3])) * rinv4[o + i];
+          LinvS[sw(o + i, o + lane)] = x[i];
+        }
+      }
+      {  // upper-right block of the inverse is zero
+        const int r = tid >> 4, c = tid & 15;
+        LinvS[sw(r, 16 + c)] = 0.0;
+      }
+      __syncthreads();
+      {
+        const int r = tid >> 4, c = tid & 15;  // M = C A^-1 (into XJ, plain 16 x 16), then -B^-1 M
+        double m = 0.0;
+#pragma unroll
+        for (int k = 0; k < 16; k++) m += D[sw(16 + r, k)] * LinvS[sw(k, c)];
+        XJ[r * 16 + c] = m;
+        __syncthreads();
+        double v = 0.0;
+#pragma unroll
+        for (int k = 0; k < 16; k++) v += LinvS[sw(16 + r, 16 + k)] * XJ[k * 16 + c];
+        LinvS[sw(16 + r, c)] = -v;
+      }
+      __syncthreads();
+      CPT(3);
+      for (int t = tid; t < kTileEl; t += kSolveThreads) a.linv[(size_t)kk * kTileEl + t] = LinvS[sw(t >> 5, t & 31)];
+      if (s_flag) {
+        failed = true;
+        if (tid == 0) a.ctrl[CTRL_FAIL_NOW] = 1;
+      }
+    };
+    // ---- prologue: the chain CTA factors and inverts tile (0,0)
+    if (is_diag) {
+      for (int t = tid; t < kTileEl; t += kSolveThreads) {
+        const int r = t >> 5, c = t & 31;
+        Dnext[sw(r, c)] = (c <= r) ? __ldcg(&H[(size_t)r * ld + c]) : 0.0;
+      }
+      __syncthreads();
+      factor_invert_publish(Dnext, 0);
+    }
+    SLV(0);
+    grid_barrier<COOP>();
+    SLV(2);
+    for (int kb = 0; kb < nblk; kb++) {
+      const int kn = kb + 1;
+      if (is_diag) {
+        // ---- chain (L_kk^-1 is still in LinvS from this CTA's own inversion)
+        double* const Araw = pipe;  // (the chain CTA does not use the ring)
+        if (kn < nblk) {
+          CPS();
+          g2s(Araw, &H[(size_t)(kn * kTile) * ld + kb * kTile], ld);
+          g2s(Dnext, &H[(size_t)(kn * kTile) * ld + kn * kTile], ld);
+          __syncthreads();
+          CPT(0);
+          cta_gemm(XI, Araw, LinvS, false);  // L_(kn,kb)
+          __syncthreads();
+          s2g(&H[(size_t)(kb * kTile) * ld + kn * kTile], ld, XI);  // mirror slot (kb, kn)
+          cta_gemm(Dnext, XI, XI, true);
+          __syncthreads();
+          CPT(1);
+          factor_invert_publish(Dnext, kn);
+          CPT(5);
+        } else {  // last step: y of the last block (row nblk has no tile left to hang it on)
+          g2s(Araw, &H[(size_t)(nblk * kTile) * ld + kb * kTile], ld);
+          __syncthreads();
+          cta_gemm(XI, Araw, LinvS, false);
+          __syncthreads();
+          if (tid < kTile) a.ybuf[kb * kTile + tid] = XI[sw(0, tid)];
+        }
+        __syncthreads();
+      } else {
+        // ---- worker: a contiguous chunk of the tiles (I,J), kb < J <= I <= nblk, J < nblk, minus (kn,kn)
+        const int rem = nblk - kb;
+        const int ncols = rem - 1;
+        const int ntri = ncols * (ncols + 1) / 2;
+        const int ntiles = ntri + ncols;
+        const long long nw = ntiles - 1;  // tile 0 = (kn,kn) is the chain's
+        const int t_lo = 1 + (int)(nw * blockIdx.x / n_work), t_hi = 1 + (int)(nw * (blockIdx.x + 1) / n_work);
+        const int nmine = ncols > 0 ? t_hi - t_lo : 0;
+        auto decode = [&](int t0, int& I, int& J) {
+          int i, j;
+          if (t0 < ntri) {
+            i = (int)((sqrt(8.0 * (double)t0 + 1.0) - 1.0) * 0.5);
+            while ((i + 1) * (i + 2) / 2 <= t0) i++;
+            while (i * (i + 1) / 2 > t0) i--;
+            j = t0 - i * (i + 1) / 2;
+          } else {
+            i = ncols;
+            j = t0 - ntri;
+          }
+          I = kb + 1 + i;
+          J = kb + 1 + j;
+        };
+        int I_iss = -1;  // row of the tile issued last
+        auto issue = [&](int n) {
+          if (n < nmine) {
+            int I, J;
+            decode(t_lo + n, I, J);
+            double* st = pipe + (n % kUpdStages) * kUpdStageDoubles;
+            const bool newrow = I != I_iss;
+            I_iss = I;
+#pragma unroll
+            for (int q = 0; q < 2; q++) {
+              const int e = tid + q * kSolveThreads, row = e >> 4, c2 = (e & 15) * 2;
+              const int so = sw(row, c2);
+              if (newrow) cp_async16(st + so, &H[(size_t)(I * kTile + row) * ld + kb * kTile + c2]);
+              if (J != I) cp_async16(st + kTileEl + so, &H[(size_t)(J * kTile + row) * ld + kb * kTile + c2]);
+              cp_async16(st + 2 * kTileEl + so, &H[(size_t)(I * kTile + row) * ld + J * kTile + c2]);
+              if (n == 0) cp_async16(LinvS + so, &a.linv[(size_t)kb * kTileEl + row * kTile + c2]);
+            }
+          }
+          cp_async_commit();
+        };
+        for (int n = 0; n < kUpdStages - 1; n++) issue(n);
+        int I_cur = -1;
+        for (int n = 0; n < nmine; n++) {
+          issue(n + kUpdStages - 1);
+          cp_async_wait<kUpdStages - 1>();
+          __syncthreads();
+          int I, J;
+          decode(t_lo + n, I, J);
+          double* st = pipe + (n % kUpdStages) * kUpdStageDoubles;
+          if (I != I_cur) {
+            I_cur = I;
+            cta_gemm(XI, st, LinvS, false);  // L_Ik
+            if (J == kn) {  // this CTA owns the first tile of the row: it publishes L_Ik
+              __syncthreads();
+              if (I < nblk) {
+                s2g(&H[(size_t)(kb * kTile) * ld + I * kTile], ld, XI);
+              } else if (tid < kTile) {
+                a.ybuf[kb * kTile + tid] = XI[sw(0, tid)];
+              }
+            }
+          }
+          const double* xj = XI;
+          if (J != I) {
+            cta_gemm(XJ, st + kTileEl, LinvS, false);  // L_Jk
+            xj = XJ;
+          }
+          __syncthreads();
+          {
+            const double* sd = st + 2 * kTileEl;
+            double acc[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
+#pragma unroll
+            for (int kk = 0; kk < 8; kk++) {
+              const int pc = (kk * 4 + t4) ^ (g << 2);
+              const double av = XI[(mi * 8 + g) * kTile + pc];
+              dmma884(acc[0][0], acc[0][1], av, xj[(ni0 * 8 + g) * kTile + pc]);
+              dmma884(acc[1][0], acc[1][1], av, xj[((ni0 + 1) * 8 + g) * kTile + pc]);
+            }
+            const int row = mi * 8 + g;
+#pragma unroll
+            for (int n2 = 0; n2 < 2; n2++) {
+              const int col = (ni0 + n2) * 8 + 2 * t4;
+              double2 d = *reinterpret_cast<const double2*>(sd + row * kTile + (col ^ (g << 2)));
+              d.x -= acc[n2][0];
+              d.y -= acc[n2][1];
+              *reinterpret_cast<double2*>(&H[(size_t)(I * kTile + row) * ld + J * kTile + col]) = d;
+            }
+          }
+          __syncthreads();
+        }
+        cp_async_wait<0>();
+        if (__ldcg(&a.ctrl[CTRL_FAIL_NOW])) failed = true;  // (a step late is early enough: read again after the loop)
+      }
+      SLV(3);
+      grid_barrier<COOP>();
+      SLV(4);
+    }
+    if (__ldcg(&a.ctrl[CTRL_FAIL_NOW])) failed = true;
+#ifdef M3R_TRACK_PROF
+    if (is_diag && tid == 0)
+      printf("V4CHAIN per step (us): load %.2f, X + SYRK %.2f, potrf %.2f, L write + invert %.2f, publish %.2f\n", cpt[0] / 1965.0 / nblk,
+             cpt[1] / 1965.0 / nblk, cpt[2] / 1965.0 / nblk, cpt[3] / 1965.0 / nblk, cpt[5] / 1965.0 / nblk);
+#endif
+  } else
   for (int kb = 0; kb < nblk; kb++) {
     if (v2) {
       // B1 (v2): L_kk into shared memory, substitution on this CTA's panel tile
@@ -846,7 +1103,7 @@ gn_solve_kernel(const SolveArgs a) {
     grid_barrier<COOP>();
     SLV(4);
   }
-  if (v2) {
+  if (v2 && !v4) {
     // the back-substitution multiplies by L_kk^-1: invert the diagonal tiles now, one per CTA, lane j = column j by
     // forward substitution (a.linv holds L_kk until here)
     for (int kb2 = blockIdx.x; kb2 < nblk; kb2 += gridDim.x) {
@@ -886,12 +1143,16 @@ gn_solve_kernel(const SolveArgs a) {
     double* sLi = &sB[0][0];                 // L_kk^-1, row-major stride 33
     for (int t = tid; t < kTile * kTile; t += kSolveThreads)
       sB[t >> 5][t & 31] = __ldcg(&a.linv[(size_t)kb * kTile * kTile + t]);
-    if (tid < kTile) s_x[kb * kTile + tid] = __ldcg(&H[(size_t)dimP * ld + kb * kTile + tid]);  // y_kb
+    if (tid < kTile)  // y_kb (v4: from ybuf; the factor's sub-diagonal tiles from their mirror slots)
+      s_x[kb * kTile + tid] = v4 ? __ldcg(&a.ybuf[kb * kTile + tid]) : __ldcg(&H[(size_t)dimP * ld + kb * kTile + tid]);
+    auto Ltile = [&](int j, int r, int cc) -> const double* {
+      return v4 ? &H[(size_t)(kb * kTile + r) * ld + j * kTile + cc] : &H[(size_t)(j * kTile + r) * ld + kb * kTile + cc];
+    };
     const int c = tid & 31, rg = tid >> 5;   // column of the tile, group of 4 rows
     double tile[4];
     if (kb + 1 < nblk) {
 #pragma unroll
-      for (int q = 0; q < 4; q++) tile[q] = __ldcg(&H[(size_t)((nblk - 1) * kTile + rg * 4 + q) * ld + kb * kTile + c]);
+      for (int q = 0; q < 4; q++) tile[q] = __ldcg(Ltile(nblk - 1, rg * 4 + q, c));
     }
     __syncthreads();
     for (int j = nblk - 1; j > kb; j--) {
@@ -900,7 +1161,7 @@ gn_solve_kernel(const SolveArgs a) {
       for (int q = 0; q < 4; q++) cur[q] = tile[q];
       if (j - 1 > kb) {  // next tile in flight while we wait for x_j
 #pragma unroll
-        for (int q = 0; q < 4; q++) tile[q] = __ldcg(&H[(size_t)((j - 1) * kTile + rg * 4 + q) * ld + kb * kTile + c]);
+        for (int q = 0; q < 4; q++) tile[q] = __ldcg(Ltile(j - 1, rg * 4 + q, c));
       }
       if (tid < 2 * kTile) {
         unsigned long long wv;
@@ -1993,10 +2254,14 @@ int launch_gn_solve(float* Twc, const GnLayout& L, const GnPtrs& P_, float delta
   static const bool no_pipe = getenv("M3R_SOLVE_NOPIPE") != nullptr;  // A/B knob: the round-1 trailing update
   if (L.nblk >= kLookaheadMinTiles && !no_pipe) {
     const int off = (L.nblk * kTile + 1) & ~1;  // 16-byte aligned behind s_x
-    const size_t dyn_pipe = sizeof(double) * ((size_t)off + (size_t)kUpdStages * kUpdStageDoubles);
+    // ring + (v4) L_kk^-1, L_Ik, L_Jk and the chain's potrf scratch
+    const size_t dyn_pipe = sizeof(double) * ((size_t)off + (size_t)kUpdStages * kUpdStageDoubles + 3 * kTile * kTile + 128);
     if (dyn_pipe <= 200 * 1024) {  // (beyond ~7000 unknowns the round-1 path runs)
       a.pipe_off = off;
       dyn = dyn_pipe;
+      static const bool no_v4 = getenv("M3R_SOLVE_NOV4") != nullptr;  // A/B knob: the two-barrier v2 step
+      a.v4 = no_v4 ? 0 : 1;
+      a.ybuf = P_.partials;  // (the accumulate's per-CTA partials are dead by now: >= 624 x 35 doubles)
     }
   }
   if (dyn > 48 * 1024 - 20 * 1024) {
