@@ -530,6 +530,15 @@ gn_solve_kernel(const SolveArgs a) {
     double* const XJ = XI + kTileEl;                              // L_Jk
     double* const colb4 = XJ + kTileEl;                           // chain: potrf column buffer (64) + 1/diag (32)
     double* const rinv4 = colb4 + 2 * kTile;
+    // chain CTA (it does not use the ring): its tiles of this step, Ak = (kb+1,kb) and Dk = (kb+1,kb+1), are in shared
+    // memory already; R = raw (kb+2,kb), T = (kb+2,kb+1) and D2 = (kb+2,kb+2) are updated with column kb by warps 4-7
+    // WHILE warp 0 factors Dk, and become the next step's Ak / Dk -- no load on the chain's critical path
+    double* Ak = pipe;
+    double* Dk = pipe + 2 * kTileEl;
+    double* const Rr = pipe + 3 * kTileEl;
+    double* Tn = pipe + 4 * kTileEl;
+    double* D2 = pipe + 5 * kTileEl;
+    double* const X2 = pipe + 6 * kTileEl;
     const int g = lane >> 2, t4 = lane & 3, mi = wrp >> 1, ni0 = (wrp & 1) * 2;
     auto g2s = [&](double* dst, const double* src, int ldsrc) {  // 32 x 32 tile -> swizzled smem, all threads
       for (int e = tid; e < kTileEl / 2; e += kSolveThreads) {
@@ -567,12 +576,14 @@ gn_solve_kernel(const SolveArgs a) {
       }
     };
     // chain CTA: factor the tile in D (swizzled), write L to H(kk,kk), invert into LinvS, publish a.linv[kk]
-    auto factor_invert_publish = [&](double* D, int kk) {
-      if (wrp == 0) {
-        const bool bad = potrf_inplace(D, rinv4, colb4, lane);
-        if (lane == 0) s_flag = bad ? 1 : 0;
+    auto factor_invert_publish = [&](double* D, int kk, bool factor) {
+      if (factor) {
+        if (wrp == 0) {
+          const bool bad = potrf_inplace(D, rinv4, colb4, lane);
+          if (lane == 0) s_flag = bad ? 1 : 0;
+        }
+        __syncthreads();
       }
-      __syncthreads();
       CPT(2);
       for (int t = tid; t < kTileEl; t += kSolveThreads) {
         const int r = t >> 5, c = t & 31;
@@ -625,7 +636,12 @@ gn_solve_kernel(const SolveArgs a) {
         Dnext[sw(r, c)] = (c <= r) ? __ldcg(&H[(size_t)r * ld + c]) : 0.0;
       }
       __syncthreads();
-      factor_invert_publish(Dnext, 0);
+      factor_invert_publish(Dnext, 0, true);
+      if (nblk > 1) {  // the chain's tiles of step 0
+        g2s(Ak, &H[(size_t)kTile * ld], ld);
+        g2s(Dk, &H[(size_t)kTile * ld + kTile], ld);
+      }
+      __syncthreads();
     }
     SLV(0);
     grid_barrier<COOP>();
@@ -634,25 +650,84 @@ gn_solve_kernel(const SolveArgs a) {
       const int kn = kb + 1;
       if (is_diag) {
         // ---- chain (L_kk^-1 is still in LinvS from this CTA's own inversion)
-        double* const Araw = pipe;  // (the chain CTA does not use the ring)
+        const int kq = kb + 2;  // kq == nblk: the rhs row
+        const int w4 = wrp - 4;
+        // OUT (=|-=) A B^T by warps 4-7 (8 rows x 32 columns each)
+        auto gemm4 = [&](double* OUT, const double* A, const double* B, bool subtract) {
+          double acc[4][2];
+#pragma unroll
+          for (int n2 = 0; n2 < 4; n2++) acc[n2][0] = acc[n2][1] = 0.0;
+#pragma unroll
+          for (int kk = 0; kk < 8; kk++) {
+            const int pc = (kk * 4 + t4) ^ (g << 2);
+            const double av = A[(w4 * 8 + g) * kTile + pc];
+#pragma unroll
+            for (int n2 = 0; n2 < 4; n2++) dmma884(acc[n2][0], acc[n2][1], av, B[(n2 * 8 + g) * kTile + pc]);
+          }
+#pragma unroll
+          for (int n2 = 0; n2 < 4; n2++) {
+            double2* d = reinterpret_cast<double2*>(OUT + (w4 * 8 + g) * kTile + ((n2 * 8 + 2 * t4) ^ (g << 2)));
+            if (subtract) {
+              double2 v = *d;
+              v.x -= acc[n2][0];
+              v.y -= acc[n2][1];
+              *d = v;
+            } else {
+              *d = make_double2(acc[n2][0], acc[n2][1]);
+            }
+          }
+        };
+        auto bar4 = [&]() { asm volatile("bar.sync 1, 128;" ::: "memory"); };
         if (kn < nblk) {
           CPS();
-          g2s(Araw, &H[(size_t)(kn * kTile) * ld + kb * kTile], ld);
-          g2s(Dnext, &H[(size_t)(kn * kTile) * ld + kn * kTile], ld);
-          __syncthreads();
+          const bool has_q = kq <= nblk, has_d2 = kq < nblk;
+          if (wrp >= 4 && has_q) {  // look-ahead tiles: in flight during the two products below
+            for (int e = tid - 128; e < kTileEl / 2; e += 128) {
+              const int r = e >> 4, c2 = (e & 15) * 2, so = sw(r, c2);
+              cp_async16(Rr + so, &H[(size_t)(kq * kTile + r) * ld + kb * kTile + c2]);
+              cp_async16(Tn + so, &H[(size_t)(kq * kTile + r) * ld + kn * kTile + c2]);
+              if (has_d2) cp_async16(D2 + so, &H[(size_t)(kq * kTile + r) * ld + kq * kTile + c2]);
+            }
+            cp_async_commit();
+          }
           CPT(0);
-          cta_gemm(XI, Araw, LinvS, false);  // L_(kn,kb)
+          cta_gemm(XI, Ak, LinvS, false);  // L_(kn,kb)
           __syncthreads();
-          s2g(&H[(size_t)(kb * kTile) * ld + kn * kTile], ld, XI);  // mirror slot (kb, kn)
-          cta_gemm(Dnext, XI, XI, true);
+          cta_gemm(Dk, XI, XI, true);
           __syncthreads();
           CPT(1);
-          factor_invert_publish(Dnext, kn);
-          CPT(5);
-        } else {  // last step: y of the last block (row nblk has no tile left to hang it on)
-          g2s(Araw, &H[(size_t)(nblk * kTile) * ld + kb * kTile], ld);
+          if (wrp == 0) {
+            const bool bad = potrf_inplace(Dk, rinv4, colb4, lane);
+            if (lane == 0) s_flag = bad ? 1 : 0;
+          } else if (wrp < 4) {  // mirror slot (kb, kn) <- L_(kn,kb)
+            for (int e = tid - 32; e < kTileEl / 2; e += 96) {
+              const int r = e >> 4, c2 = (e & 15) * 2;
+              *reinterpret_cast<double2*>(&H[(size_t)(kb * kTile + r) * ld + kn * kTile + c2]) = *reinterpret_cast<const double2*>(XI + sw(r, c2));
+            }
+          } else if (has_q) {
+            cp_async_wait<0>();
+            bar4();
+            gemm4(X2, Rr, LinvS, false);  // L_(kq,kb)
+            bar4();
+            gemm4(Tn, X2, XI, true);      // (kq,kn) -= L_(kq,kb) L_(kn,kb)^T
+            if (has_d2) gemm4(D2, X2, X2, true);
+            bar4();
+            for (int e = tid - 128; e < kTileEl / 2; e += 128) {
+              const int r = e >> 4, c2 = (e & 15) * 2;
+              // the workers of the next step read the raw tile (kq,kn) as a panel tile of column kn
+              *reinterpret_cast<double2*>(&H[(size_t)(kq * kTile + r) * ld + kn * kTile + c2]) = *reinterpret_cast<const double2*>(Tn + sw(r, c2));
+              if (has_d2)
+                *reinterpret_cast<double2*>(&H[(size_t)(kb * kTile + r) * ld + kq * kTile + c2]) = *reinterpret_cast<const double2*>(X2 + sw(r, c2));
+            }
+            if (!has_d2 && tid - 128 < kTile) a.ybuf[kb * kTile + (tid - 128)] = X2[sw(0, tid - 128)];
+          }
           __syncthreads();
-          cta_gemm(XI, Araw, LinvS, false);
+          factor_invert_publish(Dk, kn, false);
+          CPT(5);
+          { double* tmp = Ak; Ak = Tn; Tn = tmp; }
+          { double* tmp = Dk; Dk = D2; D2 = tmp; }
+        } else {  // last step: y of the last block (row nblk has no tile left to hang it on)
+          cta_gemm(XI, Ak, LinvS, false);
           __syncthreads();
           if (tid < kTile) a.ybuf[kb * kTile + tid] = XI[sw(0, tid)];
         }
@@ -663,8 +738,10 @@ gn_solve_kernel(const SolveArgs a) {
         const int ncols = rem - 1;
         const int ntri = ncols * (ncols + 1) / 2;
         const int ntiles = ntri + ncols;
-        const long long nw = ntiles - 1;  // tile 0 = (kn,kn) is the chain's
-        const int t_lo = 1 + (int)(nw * blockIdx.x / n_work), t_hi = 1 + (int)(nw * (blockIdx.x + 1) / n_work);
+        // tiles 0 = (kn,kn), 1 = (kb+2,kn) and (if it exists) 2 = (kb+2,kb+2) are the chain's
+        const int nchain = 1 + (kb + 2 <= nblk ? 1 : 0) + (kb + 2 < nblk ? 1 : 0);
+        const long long nw = ntiles > nchain ? ntiles - nchain : 0;
+        const int t_lo = nchain + (int)(nw * blockIdx.x / n_work), t_hi = nchain + (int)(nw * (blockIdx.x + 1) / n_work);
         const int nmine = ncols > 0 ? t_hi - t_lo : 0;
         auto decode = [&](int t0, int& I, int& J) {
           int i, j;
