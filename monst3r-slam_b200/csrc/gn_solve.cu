@@ -12,14 +12,14 @@
 //                 triangle and adds the incident edge blocks in edge order (deterministic, no atomics)
 //                 H_pp += A_e, H_pq -= A_e (q < p), g_p -+= b_e.  g is stored as one extra row
 //                 below H, so the factorisation also produces y = L^-1 g (bordered-matrix trick).
-//   B. Cholesky   right-looking, 32x32 tiles, fp64, two grid barriers per tile step.  From 8 tiles on (the "v2"
-//                 step, round 2) one dedicated CTA walks the serial chain -- substitution on panel tile (k+1,k),
-//                 DMMA symmetric update and one-warp LDL-ordered potrf of tile (k+1,k+1) while the others update
-//                 the trailing matrix -- every other panel tile is solved by forward substitution against L_kk
-//                 (one warp, rows in registers) and the trailing update streams its three tiles per product
-//                 through a cp.async ring into DMMA (mma.m8n8k4.f64).  Below 8 tiles (and on the round-1 fallback
-//                 path) every CTA factors + inverts the diagonal tile redundantly and the panel is a tile GEMM
-//                 with L_kk^-1.  Systems of up to 7 tiles never get here: gn_solve_resident.cu.
+//   B. Cholesky   right-looking, 32x32 tiles, fp64.  From 8 tiles on (round 2, "v4"): ONE grid barrier per tile
+//                 step.  A dedicated chain CTA factors tile (k+1,k+1) (one-warp LDL-ordered potrf), inverts it by
+//                 16x16 blocks and publishes L^-1; every other CTA owns a contiguous chunk of the trailing tiles
+//                 and forms the panel tiles it needs itself as DMMA products with L_kk^-1 (operands streamed
+//                 through a cp.async ring), writing the final L_Ik to the mirror slot in the upper triangle.
+//                 "v2" (M3R_SOLVE_NOV4=1) keeps a separate panel phase with forward substitution and two barriers
+//                 per step; below 8 tiles (and on the round-1 fallback path) every CTA factors + inverts the
+//                 diagonal tile redundantly.  Systems of up to 7 tiles never get here: gn_solve_resident.cu.
 //   C. back-substitution  L^T x = y as a barrier-free column-block dataflow over the CTAs with the L_kk^-1 tiles
 //                 (v2 forms them after the factorisation, all tiles in parallel).
 //   D. dx = -x (0 if a pivot was <= 0: gn_kernels.cu:142-150), retraction T <- Exp(dx) T in fp32
@@ -780,9 +780,11 @@ gn_solve_kernel(const SolveArgs a) {
         for (int n = 0; n < kUpdStages - 1; n++) issue(n);
         int I_cur = -1;
         for (int n = 0; n < nmine; n++) {
+          CPS();
           issue(n + kUpdStages - 1);
           cp_async_wait<kUpdStages - 1>();
           __syncthreads();
+          CPT(0);
           int I, J;
           decode(t_lo + n, I, J);
           double* st = pipe + (n % kUpdStages) * kUpdStageDoubles;
@@ -798,12 +800,14 @@ gn_solve_kernel(const SolveArgs a) {
               }
             }
           }
+          CPT(1);
           const double* xj = XI;
           if (J != I) {
             cta_gemm(XJ, st + kTileEl, LinvS, false);  // L_Jk
             xj = XJ;
           }
           __syncthreads();
+          CPT(2);
           {
             const double* sd = st + 2 * kTileEl;
             double acc[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
@@ -825,6 +829,10 @@ gn_solve_kernel(const SolveArgs a) {
             }
           }
           __syncthreads();
+          CPT(3);
+#ifdef M3R_TRACK_PROF
+          cpt[4] += 1;
+#endif
         }
         cp_async_wait<0>();
         if (__ldcg(&a.ctrl[CTRL_FAIL_NOW])) failed = true;  // (a step late is early enough: read again after the loop)
@@ -835,6 +843,9 @@ gn_solve_kernel(const SolveArgs a) {
     }
     if (__ldcg(&a.ctrl[CTRL_FAIL_NOW])) failed = true;
 #ifdef M3R_TRACK_PROF
+    if (blockIdx.x == 0 && tid == 0)
+      printf("V4WORKER per tile (us) over %lld tiles: wait %.2f, L_Ik (row changes) %.2f, L_Jk %.2f, update + write %.2f\n", cpt[4], cpt[0] / 1965.0 / cpt[4],
+             cpt[1] / 1965.0 / cpt[4], cpt[2] / 1965.0 / cpt[4], cpt[3] / 1965.0 / cpt[4]);
     if (is_diag && tid == 0)
       printf("V4CHAIN per step (us): load %.2f, X + SYRK %.2f, potrf %.2f, L write + invert %.2f, publish %.2f\n", cpt[0] / 1965.0 / nblk,
              cpt[1] / 1965.0 / nblk, cpt[2] / 1965.0 / nblk, cpt[3] / 1965.0 / nblk, cpt[5] / 1965.0 / nblk);
