@@ -1,9 +1,9 @@
 """Every solve kernel that `launch_gn_solve` can dispatch to gives the same poses.
 
-The dispatch is by system size (resident kernel up to 7 tiles, grid kernel with the v2 tile step from 8 tiles), with
-environment knobs that force the other kernels for A/B timing: M3R_SOLVE=v1 (grid kernel for small systems),
-M3R_SOLVE_NOPIPE=1 (round-1 tile step: what systems too large for the cp.async ring fall back to), M3R_SOLVE=df (the
-experimental dataflow kernel).  The knobs are read once per process, so each variant runs in its own interpreter and
+The dispatch is by system size (resident kernel up to 7 tiles, grid kernel with the single-barrier v4 tile step from 8
+tiles), with environment knobs that force the other kernels for A/B timing: M3R_SOLVE=v1 (grid kernel for small
+systems), M3R_SOLVE_NOV4=1 (the two-barrier v2 step), M3R_SOLVE_NOPIPE=1 (round-1 tile step: what systems too large
+for the cp.async ring fall back to), M3R_SOLVE=df (the experimental dataflow kernel).  The knobs are read once per process, so each variant runs in its own interpreter and
 leaves its poses in a file; all are compared with the default path's (different summation orders: 1e-5 / 1e-4 rad,
 the bar of BASELINE.json) and the default with the CPU oracle.
 """
@@ -47,7 +47,8 @@ def _run(tmp_path, tag, env, N, E):
 
 @pytest.mark.parametrize("N,E,variants", [
     (24, 80, {"grid_v1": {"M3R_SOLVE": "v1"}}),                                      # 6 tiles: resident by default
-    (72, 300, {"round1_step": {"M3R_SOLVE_NOPIPE": "1"}, "dataflow": {"M3R_SOLVE": "df"}}),  # 16 tiles: v2 by default
+    (72, 300, {"two_barrier_v2": {"M3R_SOLVE_NOV4": "1"}, "round1_step": {"M3R_SOLVE_NOPIPE": "1"},
+               "dataflow": {"M3R_SOLVE": "df"}}),                                     # 16 tiles: v4 by default
 ])
 def test_solver_variants_agree(tmp_path, oracle, synth, N, E, variants):
     need_gpu()
