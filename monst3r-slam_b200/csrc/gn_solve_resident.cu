@@ -83,9 +83,19 @@ gn_solve_resident_kernel(const ResidentSolveArgs a) {
         if (ent[u] >= 0) {
           gsum += (ent[u] & 1) ? bv[u] : -bv[u];
 #pragma unroll
-          for (int cc = 0; cc < 7; cc++) {
-            diag[cc] += v[u][cc];
-            if (oth[u] >= 0 && oth[u] < p) elem(7 * p + r, 7 * oth[u] + cc) -= v[u][cc];
+          for (int cc = 0; cc < 7; cc++) diag[cc] += v[u][cc];
+          if (oth[u] >= 0 && oth[u] < p) {
+            // seven loads, then seven stores: written as `elem -= v` the compiler has to assume the seven shared-memory
+            // addresses may alias and serialises load -> add -> store seven times per entry
+            double* ep[7];
+            double t[7];
+#pragma unroll
+            for (int cc = 0; cc < 7; cc++) {
+              ep[cc] = &elem(7 * p + r, 7 * oth[u] + cc);
+              t[cc] = *ep[cc];
+            }
+#pragma unroll
+            for (int cc = 0; cc < 7; cc++) *ep[cc] = t[cc] - v[u][cc];
           }
         }
     }
