@@ -1092,12 +1092,8 @@ gn_track_kernel(const TrackArgs ta) {
 
 template <int KIND, bool COST = false>
 int launch_track(const TrackArgs& ta, size_t dyn, cudaStream_t s) {
-  static bool attr_done = false;
-  if (!attr_done) {
-    M3R_CUDA_CHECK(cudaFuncSetAttribute(gn_track_kernel<KIND, COST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        kTrackMaxPts * kTrackPtBytes + (int)small_solve_smem_bytes(kSmallDim)));
-    attr_done = true;
-  }
+  static DynSmemOptIn opt_in;  // per kernel instantiation
+  M3R_CUDA_CHECK(opt_in.ensure(gn_track_kernel<KIND, COST>, kTrackMaxPts * kTrackPtBytes + (int)small_solve_smem_bytes(kSmallDim)));
   void* params[] = {const_cast<TrackArgs*>(&ta)};
   M3R_CUDA_CHECK(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(gn_track_kernel<KIND, COST>),
                                              dim3(ta.a.e_local * ta.cpe), dim3(kTrackThreads), params, dyn, s));
@@ -1123,12 +1119,8 @@ int launch_one(const AccumArgs& a, size_t dyn, bool pdl, cudaStream_t s) {
 template <int KIND>
 int launch_kind(const AccumArgs& a, bool staged, size_t dyn, bool pdl, cudaStream_t s) {
   if (staged) {
-    static bool attr_done = false;  // per kernel instantiation
-    if (!attr_done) {
-      M3R_CUDA_CHECK(cudaFuncSetAttribute(gn_accum_kernel<KIND, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          kMaxChunkPts * 22));
-      attr_done = true;
-    }
+    static DynSmemOptIn opt_in;  // per kernel instantiation
+    M3R_CUDA_CHECK(opt_in.ensure(gn_accum_kernel<KIND, true>, kMaxChunkPts * 22));
     return launch_one<KIND, true>(a, dyn, pdl, s);
   }
   return launch_one<KIND, false>(a, dyn, pdl, s);

@@ -258,15 +258,8 @@ size_t gn_solve_resident_smem_bytes(int nblk) {
 int launch_gn_solve_resident(const ResidentSolveArgs& a, cudaStream_t s) {
   if (a.nblk < 1 || a.nblk > kResidentMaxTiles) return M3R_ERR_UNSUPPORTED;
   const size_t dyn = gn_solve_resident_smem_bytes(a.nblk);
-  static size_t attr_set_for = 0;  // the attribute is per function (and context): raise it when a larger system shows up
-  static int attr_dev = -1;
-  int dev = 0;
-  M3R_CUDA_CHECK(cudaGetDevice(&dev));
-  if (dev != attr_dev || dyn > attr_set_for) {
-    M3R_CUDA_CHECK(cudaFuncSetAttribute(gn_solve_resident_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
-    attr_set_for = dyn;
-    attr_dev = dev;
-  }
+  static DynSmemOptIn opt_in;  // (raised when a larger system shows up)
+  M3R_CUDA_CHECK(opt_in.ensure(gn_solve_resident_kernel, (int)dyn));
   gn_solve_resident_kernel<<<1, kResThreads, dyn, s>>>(a);
   M3R_LAUNCH_CHECK();
   return M3R_OK;

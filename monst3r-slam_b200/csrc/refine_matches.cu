@@ -600,13 +600,8 @@ extern "C" int m3r_refine_matches_f16(const void* D11, const void* D21, const in
     const __half* d21 = static_cast<const __half*>(D21);
     if (radius == m3r::kStRadius && dilation_max >= 1 && dilation_max <= m3r::kStMaxLevels &&
         static_cast<long long>(n) == static_cast<long long>(h) * w) {
-      static std::once_flag once;
-      static cudaError_t attr_err = cudaSuccess;
-      std::call_once(once, [] {
-        attr_err = cudaFuncSetAttribute(m3r::refine_staged_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        m3r::kStSmemBytes);
-      });
-      M3R_CUDA_CHECK(attr_err);
+      static m3r::DynSmemOptIn opt_in;
+      M3R_CUDA_CHECK(opt_in.ensure(m3r::refine_staged_kernel, m3r::kStSmemBytes));
       const int tiles_x = (w + m3r::kTileX - 1) / m3r::kTileX, tiles_y = (h + m3r::kTileY - 1) / m3r::kTileY;
       dim3 grid(tiles_x * tiles_y, b);
       static const int reuse_ok = [] {  // debugging knob: M3R_REFINE_REUSE=0 refills the box at every level
