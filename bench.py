@@ -679,7 +679,12 @@ def run_global_opt(args, name, abi, synth, mdist, dev, rank, world, comm, barrie
     ii, jj = g["ii"][order].contiguous(), g["jj"][order].contiguous()
     parts = mdist.partition_edges(E2, world)
     lo, hi = parts[rank]
-    exchange = mdist.exchange_for_partition(parts, E2) if args.exchange == "auto" else abi.EXCHANGE_ALLREDUCE
+    exchange = mdist.exchange_for_partition(parts, E2) if args.exchange != "allreduce" else abi.EXCHANGE_ALLREDUCE
+    # equal partition: the library's own all-gather over NVLink peer memory unless NCCL is asked for (--exchange nccl)
+    xchg = None
+    if world > 1 and exchange == abi.EXCHANGE_ALLGATHER and args.exchange in ("auto", "peer"):
+        xchg = mdist.init_peer_exchange(rank, world, E2)
+        exchange = abi.EXCHANGE_PEER
     own = order[lo:hi]
     idx, valid, Q = g["idx"][own].contiguous(), g["valid"][own].contiguous(), g["Q"][own].contiguous()
     full = None
@@ -687,7 +692,7 @@ def run_global_opt(args, name, abi, synth, mdist, dev, rank, world, comm, barrie
         full = (g["idx"][order].contiguous(), g["valid"][order].contiguous(), g["Q"][order].contiguous())
     del g["idx"], g["valid"], g["Q"]
     torch.cuda.empty_cache()
-    shard = mdist.make_shard(lo, hi, comm, exchange) if world > 1 else None
+    shard = mdist.make_shard(lo, hi, comm, exchange, xchg) if world > 1 else None
     iters = 10
     if cfg["calib"]:
         prm = abi.make_params(abi.GN_CALIB, 1.0, 10.0, 0.0, 1.5, iters, 0.0, H, W, -10, 1e-6)
@@ -776,6 +781,8 @@ def run_global_opt(args, name, abi, synth, mdist, dev, rank, world, comm, barrie
         identical = bool(torch.equal(T1, T_sharded))
         del ws1, full
     barrier()
+    if xchg is not None:
+        mdist.destroy_peer_exchange(xchg)
     torch.cuda.empty_cache()
     return {"config": f"configs[{cfg['configs_index']}]: {N} keyframes / {E2} directed edges, 512x384, "
                       f"{'gauss_newton_calib' if cfg['calib'] else 'gauss_newton_rays'} x{iters} iters",
@@ -790,9 +797,11 @@ def run_global_opt(args, name, abi, synth, mdist, dev, rank, world, comm, barrie
             "accumulate_streamed_bytes_per_rank": 8 * (hi - lo) * n + 12 * touched * n,
             "solve_alone_ms": solve_ms, "solve_dim": 7 * (N - 1),
             "solve_and_comm_ms_per_iter": (ms - pack_ms) / iters - acc_ms,
-            "collective": (("in-place ncclAllGather(f64) of the [E2,56] edge blocks (equal contiguous edge ranges), once per iteration"
-                           if exchange == abi.EXCHANGE_ALLGATHER else
-                           "ncclAllReduce(sum, f64) of the zero-padded [E2,56] edge blocks, once per iteration") if world > 1 else None),
+            "collective": (({abi.EXCHANGE_PEER: "own kernel: all-gather of the [E2,56] fp64 edge blocks by 16-byte stores into the peers' buffers over "
+                                                "NVLink (CUDA IPC) + release/acquire flags, once per iteration, no NCCL on the data path",
+                             abi.EXCHANGE_ALLGATHER: "in-place ncclAllGather(f64) of the [E2,56] edge blocks (equal contiguous edge ranges), once per iteration",
+                             abi.EXCHANGE_ALLREDUCE: "ncclAllReduce(sum, f64) of the zero-padded [E2,56] edge blocks, once per iteration"}[exchange])
+                           if world > 1 else None),
             "poses_bit_identical_to_unsharded": identical, "poses_identical_on_all_ranks": same_on_all_ranks,
             "poses_sha1": sha, "max_abs_pose_err_vs_gt": gerr,
             "working_set": "13 B/pt/edge slabs (>= 0.6 GB per rank at c3/8) exceed the 126 MB L2; not flushed"}
@@ -1253,7 +1262,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--global-opt", default="both", choices=["both", "c3", "c4", "none"])
-    ap.add_argument("--exchange", default="auto", choices=["auto", "allreduce"],
+    ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "nccl", "allreduce"],
                     help="edge-block exchange at N > 1: auto = all-gather when the partition is equal, else all-reduce")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-sequence", action="store_true")

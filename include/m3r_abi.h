@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define M3R_ABI_VERSION 3
+#define M3R_ABI_VERSION 4
 
 /* status codes */
 #define M3R_OK 0
@@ -124,14 +124,20 @@ int m3r_match_fused(const float* X11, const float* X21, const void* D11, const v
  *                           only for the equal partition: world | num_edges and rank r owns
  *                           [r * num_edges / world, (r + 1) * num_edges / world).  A rank whose range is not
  *                           that returns M3R_ERR_BAD_ARG before anything is enqueued.
+ *   M3R_EXCHANGE_PEER       no NCCL: the library's own all-gather kernel over NVLink peer memory (m3r_xchg_*
+ *                           below; `xchg` must be a connected exchange, `comm` is ignored).  Same equal-partition
+ *                           rule as ALLGATHER.  The edge blocks of iteration it live in parity it & 1 of the
+ *                           exchange buffer instead of the workspace (m3r_gn_edge_blocks / export do not see them).
  * dist.exchange_for_partition() derives the value from the global partition, which every rank knows. */
 #define M3R_EXCHANGE_ALLREDUCE 0
 #define M3R_EXCHANGE_ALLGATHER 1
+#define M3R_EXCHANGE_PEER 2
 typedef struct m3r_gn_shard {
   int edge_lo;
   int edge_hi;
   void* comm;
-  int exchange; /* M3R_EXCHANGE_*; ignored when comm == NULL */
+  int exchange; /* M3R_EXCHANGE_*; ignored when comm == NULL and xchg == NULL */
+  void* xchg;   /* M3R_EXCHANGE_PEER: from m3r_xchg_create + m3r_xchg_connect; NULL otherwise (ABI v4) */
 } m3r_gn_shard;
 
 typedef struct m3r_gn_params {
@@ -258,6 +264,20 @@ int m3r_comm_init(int rank, int world, const void* id /* 128 bytes, host */, voi
 int m3r_comm_destroy(void* comm);
 /* in-place sum all-reduce of `count` doubles (used by the GN loop; exposed for tests) */
 int m3r_comm_allreduce_f64(void* comm, double* buf, size_t count, void* stream);
+
+/* Peer-memory exchange (no counterpart in the reference, which is single-GPU; replaces the NCCL call of the sharded
+ * Gauss-Newton loop by ONE kernel of this library: 16-byte stores into every peer's buffer over NVLink, a
+ * release/acquire flag per peer, csrc/peer_exchange.cu).  One process per GPU on one node:
+ *   m3r_xchg_create   allocates this rank's exchange buffer (2 x capacity_bytes + flags, cudaMalloc -- set-up time,
+ *                     not the hot path) on the current device and returns its 64-byte CUDA IPC handle (host memory);
+ *                     capacity_bytes >= num_edges * 56 * 8 of the largest graph to be solved.
+ *   m3r_xchg_connect  takes the `world` handles in rank order (exchanged by the caller, e.g. torch.distributed
+ *                     all_gather) and maps the peers' buffers (needs P2P access between the GPUs).
+ *   m3r_xchg_destroy  after a barrier across the ranks (a peer may still be writing otherwise). */
+#define M3R_IPC_HANDLE_BYTES 64
+int m3r_xchg_create(size_t capacity_bytes, void** xchg_out, void* ipc_handle_out /* 64 bytes, host */);
+int m3r_xchg_connect(void* xchg, int rank, int world, const void* all_handles /* world x 64 bytes, host */);
+int m3r_xchg_destroy(void* xchg);
 
 #ifdef __cplusplus
 }

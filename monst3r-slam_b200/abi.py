@@ -26,6 +26,7 @@ EXPORTS = [
     "m3r_gn_export_hs_gs", "m3r_pose_retr", "m3r_comm_unique_id", "m3r_comm_init", "m3r_comm_destroy",
     "m3r_comm_allreduce_f64", "m3r_edge_admit", "m3r_constrain_points_to_ray",
     "m3r_track_frame", "m3r_track_workspace_bytes", "m3r_iter_proj_static", "m3r_iter_proj_static_max_texels",
+    "m3r_xchg_create", "m3r_xchg_connect", "m3r_xchg_destroy",
 ]
 
 
@@ -43,10 +44,12 @@ class TrackParams(C.Structure):
 
 
 class GnShard(C.Structure):
-    _fields_ = [("edge_lo", C.c_int), ("edge_hi", C.c_int), ("comm", C.c_void_p), ("exchange", C.c_int)]
+    _fields_ = [("edge_lo", C.c_int), ("edge_hi", C.c_int), ("comm", C.c_void_p), ("exchange", C.c_int),
+                ("xchg", C.c_void_p)]
 
 
-EXCHANGE_ALLREDUCE, EXCHANGE_ALLGATHER = 0, 1
+EXCHANGE_ALLREDUCE, EXCHANGE_ALLGATHER, EXCHANGE_PEER = 0, 1, 2
+IPC_HANDLE_BYTES = 64
 
 
 def _load():
@@ -364,3 +367,22 @@ def track_frame(T_WCf, T_WCk, Xf, Xk, valid, Q, K, params, workspace=None):
                                int(n), C.byref(params), _ptr(dx), _ptr(info), _ptr(workspace),
                                C.c_size_t(workspace.numel()), _stream()), "m3r_track_frame")
     return T_rel, dx, info
+
+
+# ---- peer-memory exchange of the sharded Gauss-Newton loop (m3r_abi.h: m3r_xchg_*) -----------------------------
+def xchg_create(capacity_bytes):
+    """-> (handle c_void_p, 64-byte CUDA IPC handle of this rank's exchange buffer on the current device)"""
+    x = C.c_void_p(0)
+    buf = C.create_string_buffer(IPC_HANDLE_BYTES)
+    _check(lib.m3r_xchg_create(C.c_size_t(int(capacity_bytes)), C.byref(x), buf), "m3r_xchg_create")
+    return x, bytes(buf.raw)
+
+
+def xchg_connect(x, rank, world, handles):
+    """handles: the `world` 64-byte IPC handles in rank order"""
+    assert len(handles) == world and all(len(h) == IPC_HANDLE_BYTES for h in handles)
+    _check(lib.m3r_xchg_connect(x, int(rank), int(world), b"".join(handles)), "m3r_xchg_connect")
+
+
+def xchg_destroy(x):
+    _check(lib.m3r_xchg_destroy(x), "m3r_xchg_destroy")

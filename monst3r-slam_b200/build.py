@@ -16,7 +16,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, os.environ.get("M3R_LIB_DIR", "lib"))  # M3R_LIB_DIR: side-by-side variant builds for A/B timing
 INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 
-CU_SOURCES = ["iter_proj.cu", "refine_matches.cu", "gn_accum.cu", "gn_solve.cu", "gn_solve_resident.cu", "gn_driver.cu", "edge_store.cu", "frame_track.cu"]
+CU_SOURCES = ["iter_proj.cu", "refine_matches.cu", "gn_accum.cu", "gn_solve.cu", "gn_solve_resident.cu", "gn_driver.cu", "edge_store.cu", "frame_track.cu", "peer_exchange.cu"]
 HEADERS = ["common.cuh", "gn_common.cuh", "tma.cuh", "gn_device.cuh", "gn_tile.cuh"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--expt-relaxed-constexpr"]

@@ -200,6 +200,11 @@ struct ResidentSolveArgs {
   float delta_thresh;
 };
 int launch_gn_solve_resident(const ResidentSolveArgs& a, cudaStream_t s);
+// peer-memory all-gather of the edge blocks (peer_exchange.cu)
+int peer_xchg_check(const void* xchg, int num_edges, int lo, int hi);
+unsigned peer_xchg_next_seq(void* xchg);
+double* peer_xchg_buffer(void* xchg, int parity);
+int launch_peer_allgather(void* xchg, int lo, int hi, int it, unsigned seq, int* ctrl, cudaStream_t s);
 int launch_export_hs_gs(const GnLayout& L, const GnPtrs& P, float* Hs, float* gs, cudaStream_t s);
 int launch_pose_retr(float* Twc, const float* dx, int num_kf, int num_fix, cudaStream_t s);
 

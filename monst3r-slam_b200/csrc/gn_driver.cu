@@ -117,6 +117,10 @@ int shard_range(const m3r_gn_shard* shard, int num_edges, int* lo, int* hi) {
 // partition): zero the foreign slots and sum-all-reduce (exact, a sum with zeros).
 // -> 1 all-gather, 0 all-reduce, < 0 error (an ALLGATHER request this rank's range does not satisfy)
 int exchange_mode(const m3r_gn_shard* shard, int num_edges, int lo, int hi) {
+  if (shard && shard->exchange == M3R_EXCHANGE_PEER) {  // -> 2: the library's own all-gather over peer memory
+    const int rc = peer_xchg_check(shard->xchg, num_edges, lo, hi);
+    return rc == M3R_OK ? 2 : rc;
+  }
   if (!shard || !shard->comm) return 0;
   if (shard->exchange == M3R_EXCHANGE_ALLREDUCE) return 0;
   if (shard->exchange != M3R_EXCHANGE_ALLGATHER) return M3R_ERR_BAD_ARG;
@@ -132,10 +136,10 @@ int exchange_mode(const m3r_gn_shard* shard, int num_edges, int lo, int hi) {
 
 int accumulate_step(const float* Twc, const float* Xs, const float* K, const GnLayout& L, const GnPtrs& P,
                     const m3r_gn_params& prm, const m3r_gn_shard* shard, int lo, int hi, const GnFuse& fuse,
-                    cudaStream_t s) {
+                    cudaStream_t s, int it = 0, unsigned xchg_seq = 0) {
   const int mode = exchange_mode(shard, L.num_edges, lo, hi);
   if (mode < 0) {
-    set_last_error_text("m3r_gn_shard: exchange = ALLGATHER needs the equal partition (world | num_edges, rank-ordered ranges)");
+    set_last_error_text("m3r_gn_shard: exchange = ALLGATHER / PEER needs the equal partition (world | num_edges, rank-ordered ranges) and, for PEER, a connected exchange of sufficient capacity");
     return mode;
   }
   const bool gather = mode == 1;
@@ -148,6 +152,7 @@ int accumulate_step(const float* Twc, const float* Xs, const float* K, const GnL
   }
   int rc = launch_gn_accumulate(Twc, Xs, K, L, P, prm, lo, hi, fuse, s);
   if (rc != M3R_OK) return rc;
+  if (mode == 2) return launch_peer_allgather(shard->xchg, lo, hi, it, xchg_seq, P.ctrl, s);  // (P.eb is the exchange buffer)
   if (gather) {
     const size_t count = (size_t)(hi - lo) * kEdgeBlock;
     const int nrc = nccl().AllGather(P.eb + (size_t)lo * kEdgeBlock, P.eb, count, kNcclFloat64, shard->comm, s);
@@ -209,6 +214,10 @@ extern "C" int m3r_gn_accumulate(const float* Twc, const float* Xs, const float*
   int lo, hi;
   rc = shard_range(shard, num_edges, &lo, &hi);
   if (rc != M3R_OK) return rc;
+  if (shard && shard->exchange == M3R_EXCHANGE_PEER) {
+    set_last_error_text("m3r_gn_accumulate: the peer exchange keeps its edge blocks in the exchange buffer; use m3r_gauss_newton");
+    return M3R_ERR_UNSUPPORTED;
+  }
   GnFuse nofuse{};
   return accumulate_step(Twc, Xs, K, L, gn_ptrs(L, workspace), *params, shard, lo, hi, nofuse,
                          static_cast<cudaStream_t>(stream));
@@ -259,16 +268,18 @@ extern "C" int m3r_gauss_newton(float* Twc, const float* Xs, const float* Cs, co
   int lo, hi;
   rc = shard_range(shard, num_edges, &lo, &hi);
   if (rc != M3R_OK) return rc;
-  if (exchange_mode(shard, num_edges, lo, hi) < 0) {  // before anything is enqueued
-    set_last_error_text("m3r_gn_shard: exchange = ALLGATHER needs the equal partition (world | num_edges, rank-ordered ranges)");
+  const int xmode = exchange_mode(shard, num_edges, lo, hi);
+  if (xmode < 0) {  // before anything is enqueued
+    set_last_error_text("m3r_gn_shard: exchange = ALLGATHER / PEER needs the equal partition (world | num_edges, rank-ordered ranges) and, for PEER, a connected exchange of sufficient capacity");
     return M3R_ERR_BAD_ARG;
   }
+  const unsigned xchg_seq = xmode == 2 ? peer_xchg_next_seq(shard->xchg) : 0u;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   GnPtrs P = gn_ptrs(L, workspace);
   // small systems without a collective: solve + retract ride in the accumulate kernel (1 launch / iteration)
   GnFuse fuse{};
   fuse.Twc = Twc; fuse.dx_out = dx_out; fuse.info_out = info_out; fuse.delta_thresh = params->delta_thresh;
-  fuse.enabled = (L.dim <= kSmallDim) && !(shard && shard->comm) && lo == 0 && hi == num_edges;
+  fuse.enabled = (L.dim <= kSmallDim) && !(shard && (shard->comm || xmode == 2)) && lo == 0 && hi == num_edges;
   const unsigned ll_epoch = (params->max_iter > 0 && fuse.enabled) ? gn_next_epoch() : 0u;
   rc = launch_gn_prepare(ii, jj, L, P, s, dx_out, kPose * (num_kf - 1), info_out, ll_epoch);  // also zeroes dx_out / info_out
   if (rc != M3R_OK) return rc;
@@ -285,10 +296,12 @@ extern "C" int m3r_gauss_newton(float* Twc, const float* Xs, const float* Cs, co
   }
   for (int it = 0; it < params->max_iter; it++) {
     fuse.pdl = fuse.enabled && it > 0;  // iteration 0 follows pack: full serialisation
-    rc = accumulate_step(Twc, Xs, K, L, P, *params, shard, lo, hi, fuse, s);
+    GnPtrs Pit = P;
+    if (xmode == 2) Pit.eb = peer_xchg_buffer(shard->xchg, it);  // the edge blocks of this iteration live in the exchange buffer
+    rc = accumulate_step(Twc, Xs, K, L, Pit, *params, shard, lo, hi, fuse, s, it, xchg_seq);
     if (rc != M3R_OK) return rc;
     if (!fuse.enabled) {
-      rc = launch_gn_solve(Twc, L, P, params->delta_thresh, dx_out, info_out, s);
+      rc = launch_gn_solve(Twc, L, Pit, params->delta_thresh, dx_out, info_out, s);
       if (rc != M3R_OK) return rc;
     }
   }

@@ -71,7 +71,33 @@ def exchange_for_partition(parts, num_edges):
     return abi.EXCHANGE_ALLGATHER if ok else abi.EXCHANGE_ALLREDUCE
 
 
-def make_shard(lo, hi, comm=None, exchange=0):
-    """`exchange` must be the same on every rank: take it from exchange_for_partition(all ranks' ranges)."""
+def make_shard(lo, hi, comm=None, exchange=0, xchg=None):
+    """`exchange` must be the same on every rank: take it from exchange_for_partition(all ranks' ranges)
+    (abi.EXCHANGE_PEER with `xchg` from init_peer_exchange when the partition is the equal one)."""
     from . import abi
-    return abi.GnShard(int(lo), int(hi), comm if comm is not None else C.c_void_p(0), int(exchange))
+    return abi.GnShard(int(lo), int(hi), comm if comm is not None else C.c_void_p(0), int(exchange),
+                       xchg if xchg is not None else C.c_void_p(0))
+
+
+def init_peer_exchange(rank, world, max_directed_edges, group=None):
+    """The library's own all-gather of the edge blocks over NVLink peer memory (csrc/peer_exchange.cu): every rank
+    allocates an exchange buffer for graphs of up to `max_directed_edges` edges, the 64-byte CUDA IPC handles go
+    round with torch.distributed (any backend), every rank maps its peers' buffers.  One process per GPU, one node.
+    -> handle for make_shard(..., exchange=abi.EXCHANGE_PEER, xchg=handle); destroy_peer_exchange() when done."""
+    import torch.distributed as dist
+    from . import abi
+    x, mine = abi.xchg_create(int(max_directed_edges) * 56 * 8)
+    handles = [None] * world
+    dist.all_gather_object(handles, mine, group=group)
+    abi.xchg_connect(x, rank, world, handles)
+    dist.barrier(group=group)  # nobody pushes before everybody is connected
+    return x
+
+
+def destroy_peer_exchange(x, group=None):
+    import torch
+    import torch.distributed as dist
+    from . import abi
+    torch.cuda.synchronize()
+    dist.barrier(group=group)  # a peer may still be writing into this rank's buffer otherwise
+    abi.xchg_destroy(x)

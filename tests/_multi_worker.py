@@ -97,6 +97,28 @@ def main():
                                     valid[lo:hi].contiguous(), Q[lo:hi].contiguous(), shard=sh, workspace=ws)
         torch.cuda.synchronize()
         record(name, Twc, dx, [int(v) for v in info.cpu().tolist()])
+    # the library's own all-gather over NVLink peer memory (no NCCL on the data path): two solves in a row (the second
+    # re-uses both parities of the exchange buffer with the next solve's epochs), and a request it must refuse
+    xchg = mdist.init_peer_exchange(rank, world, E2)
+    lo, hi = parts[rank]
+    sh = mdist.make_shard(lo, hi, None, abi.EXCHANGE_PEER, xchg)
+    ws, _ = abi.gn_workspace(40, E2, 3000, dev, edges_local=hi - lo)
+    for name in ("cabi_equal_peer", "cabi_equal_peer_again"):
+        Twc = g["Twc"].clone()
+        dx, info = abi.gauss_newton(prm, Twc, g["Xs"], g["Cs"], None, ii, jj, idx[lo:hi].contiguous(),
+                                    valid[lo:hi].contiguous(), Q[lo:hi].contiguous(), shard=sh, workspace=ws)
+        torch.cuda.synchronize()
+        record(name, Twc, dx, [int(v) for v in info.cpu().tolist()])
+    try:
+        ulo, uhi = uneven[rank]
+        abi.gauss_newton(prm, g["Twc"].clone(), g["Xs"], g["Cs"], None, ii, jj, idx[ulo:uhi].contiguous(), valid[ulo:uhi].contiguous(),
+                         Q[ulo:uhi].contiguous(), shard=mdist.make_shard(ulo, uhi, None, abi.EXCHANGE_PEER, xchg),
+                         workspace=abi.gn_workspace(40, E2, 3000, dev, edges_local=uhi - ulo)[0])
+        out["cases"]["peer_on_uneven_rejected"] = False
+    except abi.M3RError:
+        out["cases"]["peer_on_uneven_rejected"] = True
+    torch.cuda.synchronize()
+    mdist.destroy_peer_exchange(xchg)
     # stand-alone m3r_comm_allreduce_f64
     buf = torch.arange(1000, dtype=torch.float64, device=dev) * (rank + 1)
     abi._check(abi.lib.m3r_comm_allreduce_f64(comm, abi._ptr(buf), abi.C.c_size_t(buf.numel()), abi._stream()),

@@ -23,7 +23,7 @@ def test_library_exports_every_declared_symbol(abi):
     for s in syms:
         assert hasattr(abi.lib, s), s
     assert set(syms) == set(abi.EXPORTS)
-    assert abi.lib.m3r_abi_version() == 3
+    assert abi.lib.m3r_abi_version() == 4
 
 
 def test_workspace_size_is_monotone(abi):

@@ -30,7 +30,7 @@ def test_two_rank_sharded_solve_bit_identical_to_unsharded():
         assert r["unsharded_info"][:2] == [10, 0]
         assert r["auto_exchange"] == "allgather"
         for name in ("pybind_equal_allgather", "pybind_equal_allreduce", "pybind_uneven_allreduce", "cabi_equal_allgather",
-                     "cabi_uneven_allreduce"):
+                     "cabi_uneven_allreduce", "cabi_equal_peer", "cabi_equal_peer_again"):
             c = r["cases"][name]
             assert c["bit_identical_to_unsharded"] and c["identical_across_ranks"], (name, c)
             assert c["info"][:2] == [10, 0], (name, c)
@@ -38,4 +38,5 @@ def test_two_rank_sharded_solve_bit_identical_to_unsharded():
         assert ss["global_pairs"] == 90 and ss["local_pairs"] == 45 and ss["identical_across_ranks"], ss
         assert ss["max_abs_diff_vs_single_device_graph"] < 1e-5 and ss["moved"] > 1e-3, ss
         assert r["cases"]["allgather_on_uneven_rejected"] is True
+        assert r["cases"]["peer_on_uneven_rejected"] is True
         assert r["cases"]["comm_allreduce_f64_exact"] is True
