@@ -7,10 +7,10 @@
 // Every rank owns an exchange buffer allocated by the library (cudaMalloc, so it can be shared by CUDA IPC whatever
 // allocator the caller uses): two parity buffers of the full [E2, 56] fp64 edge-block array + two rows of flags.
 // The accumulate kernel of iteration `it` writes this rank's blocks into parity it & 1 of its OWN buffer; then
-// peer_allgather_kernel (one CTA)
-//   1. copies them into the same slots of every peer's buffer with 16-byte stores over NVLink,
-//   2. fence.sys, then st.release.sys of this solve's epoch into flag[parity][rank] on every peer,
-//   3. waits (ld.acquire.sys) until every peer's flag in its own buffer carries the epoch.
+// peer_allgather_kernel (one CTA per peer)
+//   1. copies them into the same slots of the peer's buffer with 16-byte stores over NVLink,
+//   2. fence.sys, then st.release.sys of this solve's epoch into flag[parity][rank] on the peer,
+//   3. waits (ld.acquire.sys) until the peer's flag in its own buffer carries the epoch.
 // When the kernel retires the local buffer holds all blocks and the solve that follows on the stream reads it.
 // Two parities suffice: a rank can only push iteration it+1 after its own solve of iteration it, which needed every
 // peer's blocks of iteration it, which a peer only pushes after ITS solve of iteration it-1 -- so nobody still reads
@@ -53,19 +53,18 @@ __device__ __forceinline__ int ld_acquire_sys(const int* p) {
 __global__ void __launch_bounds__(1024)
 peer_allgather_kernel(const PushArgs a) {
   if (a.ctrl[CTRL_DONE]) return;  // (identical on every rank: the stop test runs on identical data)
+  // one CTA per peer: push this rank's blocks into the peer's buffer, raise our flag there, wait for the peer's flag here
   const int tid = threadIdx.x;
+  const int r = (int)blockIdx.x + ((int)blockIdx.x >= a.rank ? 1 : 0);
   const uint4* src = reinterpret_cast<const uint4*>(a.peer[a.rank] + (size_t)a.parity * a.slot_bytes + a.off);
+  uint4* dst = reinterpret_cast<uint4*>(a.peer[r] + (size_t)a.parity * a.slot_bytes + a.off);
   const size_t n16 = a.nbytes / 16;
-  for (int r = 0; r < a.world; r++) {
-    if (r == a.rank) continue;
-    uint4* dst = reinterpret_cast<uint4*>(a.peer[r] + (size_t)a.parity * a.slot_bytes + a.off);
-    for (size_t k = tid; k < n16; k += blockDim.x) dst[k] = src[k];
-  }
+  for (size_t k = tid; k < n16; k += blockDim.x) dst[k] = src[k];
   __syncthreads();
-  if (tid < a.world && tid != a.rank) {
+  if (tid == 0) {
     __threadfence_system();
-    st_release_sys(reinterpret_cast<int*>(a.peer[tid] + 2 * a.slot_bytes) + a.parity * kFlagStride + a.rank, a.epoch);
-    const int* f = reinterpret_cast<const int*>(a.peer[a.rank] + 2 * a.slot_bytes) + a.parity * kFlagStride + tid;
+    st_release_sys(reinterpret_cast<int*>(a.peer[r] + 2 * a.slot_bytes) + a.parity * kFlagStride + a.rank, a.epoch);
+    const int* f = reinterpret_cast<const int*>(a.peer[a.rank] + 2 * a.slot_bytes) + a.parity * kFlagStride + r;
     long long spins = 0;
     while ((int)(ld_acquire_sys(f) - a.epoch) < 0) {
       if (++spins > (1ll << 27)) {  // seconds: a peer is gone
@@ -106,7 +105,7 @@ int launch_peer_allgather(void* x, int lo, int hi, int it, unsigned seq, int* ct
   a.off = (unsigned long long)lo * kEdgeBlock * sizeof(double);
   a.nbytes = (unsigned long long)(hi - lo) * kEdgeBlock * sizeof(double);  // 448 B per edge: a multiple of 16
   a.ctrl = ctrl;
-  peer_allgather_kernel<<<1, 1024, 0, s>>>(a);
+  peer_allgather_kernel<<<p->world - 1, 1024, 0, s>>>(a);
   M3R_LAUNCH_CHECK();
   return M3R_OK;
 }
