@@ -7,6 +7,7 @@
 // iterations turn into no-ops, so there is no host synchronisation anywhere in the loop.
 #include <dlfcn.h>
 
+#include <cstdlib>
 #include <cstring>
 #include <cstdint>
 #include <mutex>
@@ -152,7 +153,7 @@ int accumulate_step(const float* Twc, const float* Xs, const float* K, const GnL
   }
   int rc = launch_gn_accumulate(Twc, Xs, K, L, P, prm, lo, hi, fuse, s);
   if (rc != M3R_OK) return rc;
-  if (mode == 2) return launch_peer_allgather(shard->xchg, lo, hi, it, xchg_seq, P.ctrl, s);  // (P.eb is the exchange buffer)
+  if (mode == 2) return launch_peer_allgather(shard->xchg, lo, hi, it, xchg_seq, P.ctrl, s);  // (P.eb is this rank's exchange buffer)
   if (gather) {
     const size_t count = (size_t)(hi - lo) * kEdgeBlock;
     const int nrc = nccl().AllGather(P.eb + (size_t)lo * kEdgeBlock, P.eb, count, kNcclFloat64, shard->comm, s);

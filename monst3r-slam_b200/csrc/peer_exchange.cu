@@ -60,6 +60,11 @@ peer_allgather_kernel(const PushArgs a) {
   uint4* dst = reinterpret_cast<uint4*>(a.peer[r] + (size_t)a.parity * a.slot_bytes + a.off);
   const size_t n16 = a.nbytes / 16;
   for (size_t k = tid; k < n16; k += blockDim.x) dst[k] = src[k];
+  // EVERY storing thread fences before the barrier.  Measured on 2 x B200: with only the flag-writing thread fencing
+  // after the barrier (the usual "barrier; thread 0: fence, flag" idiom) the flag overtook other warps' NVLink stores
+  // about every second time two ranks pushed at the same moment -- the receiver then solved with the peer's blocks of
+  // two iterations earlier (3 of 3 runs of tests/test_gpu_multi.py failed, 8 of 8 pass with this line).
+  __threadfence_system();
   __syncthreads();
   if (tid == 0) {
     __threadfence_system();
@@ -89,6 +94,7 @@ int peer_xchg_check(const void* x, int num_edges, int lo, int hi) {
   return M3R_OK;
 }
 unsigned peer_xchg_next_seq(void* x) { return ++static_cast<PeerXchg*>(x)->seq; }
+static int peer_epoch(unsigned seq, int it) { return (int)(((seq & 0x7ffffu) << 12) | (unsigned)((it + 1) & 0xfff)); }
 double* peer_xchg_buffer(void* x, int parity) {
   PeerXchg* p = static_cast<PeerXchg*>(x);
   return reinterpret_cast<double*>(p->local + (size_t)(parity & 1) * p->slot_bytes);
@@ -100,7 +106,7 @@ int launch_peer_allgather(void* x, int lo, int hi, int it, unsigned seq, int* ct
   a.rank = p->rank;
   a.world = p->world;
   a.parity = it & 1;
-  a.epoch = (int)(((seq & 0x7ffffu) << 12) | (unsigned)((it + 1) & 0xfff));
+  a.epoch = peer_epoch(seq, it);
   a.slot_bytes = p->slot_bytes;
   a.off = (unsigned long long)lo * kEdgeBlock * sizeof(double);
   a.nbytes = (unsigned long long)(hi - lo) * kEdgeBlock * sizeof(double);  // 448 B per edge: a multiple of 16

@@ -30,7 +30,7 @@ def test_two_rank_sharded_solve_bit_identical_to_unsharded():
         assert r["unsharded_info"][:2] == [10, 0]
         assert r["auto_exchange"] == "allgather"
         for name in ("pybind_equal_allgather", "pybind_equal_allreduce", "pybind_uneven_allreduce", "cabi_equal_allgather",
-                     "cabi_uneven_allreduce", "cabi_equal_peer", "cabi_equal_peer_again"):
+                     "cabi_uneven_allreduce", "cabi_equal_peer", "cabi_equal_peer_again", "cabi_equal_peer_3", "cabi_equal_peer_4"):
             c = r["cases"][name]
             assert c["bit_identical_to_unsharded"] and c["identical_across_ranks"], (name, c)
             assert c["info"][:2] == [10, 0], (name, c)
