@@ -680,9 +680,10 @@ def run_global_opt(args, name, abi, synth, mdist, dev, rank, world, comm, barrie
     parts = mdist.partition_edges(E2, world)
     lo, hi = parts[rank]
     exchange = mdist.exchange_for_partition(parts, E2) if args.exchange != "allreduce" else abi.EXCHANGE_ALLREDUCE
-    # equal partition: the library's own all-gather over NVLink peer memory unless NCCL is asked for (--exchange nccl)
+    # --exchange peer: the library's own all-gather kernel over NVLink peer memory instead of ncclAllGather (A/B on 2 and 8
+    # GPUs: a tie to 3 % slower, profiles/r02peer_*; the NCCL call stays the default)
     xchg = None
-    if world > 1 and exchange == abi.EXCHANGE_ALLGATHER and args.exchange in ("auto", "peer"):
+    if world > 1 and exchange == abi.EXCHANGE_ALLGATHER and args.exchange == "peer":
         xchg = mdist.init_peer_exchange(rank, world, E2)
         exchange = abi.EXCHANGE_PEER
     own = order[lo:hi]
