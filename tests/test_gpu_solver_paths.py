@@ -47,6 +47,7 @@ def _run(tmp_path, tag, env, N, E):
 
 @pytest.mark.parametrize("N,E,variants", [
     (24, 80, {"grid_v1": {"M3R_SOLVE": "v1"}}),                                      # 6 tiles: resident by default
+    (35, 120, {"two_barrier_v2": {"M3R_SOLVE_NOV4": "1"}}),                          # 8 tiles: the smallest v4 system
     (72, 300, {"two_barrier_v2": {"M3R_SOLVE_NOV4": "1"}, "round1_step": {"M3R_SOLVE_NOPIPE": "1"},
                "dataflow": {"M3R_SOLVE": "df"}}),                                     # 16 tiles: v4 by default
 ])
